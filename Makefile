@@ -1,0 +1,36 @@
+# Build for NVIDIA B200 (sm_100a) only.  Mirrors the reference's Makefile targets
+# (/root/reference/Makefile:22-33: build/libflash_attention.so + build/tests) with nvcc
+# instead of g++/Poplar.  No Triton, no multi-arch fatbins, no CPU fallback.
+NVCC    ?= nvcc
+CC      ?= gcc
+ARCH    ?= -gencode arch=compute_100a,code=sm_100a
+OUT     ?= build
+NVFLAGS ?= -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-Wall -Xptxas -v
+CSRC    := flash_attention_ipu_b200/csrc
+HDRS    := $(wildcard $(CSRC)/*.cuh) include/fa_b200.h
+
+all: $(OUT)/libflash_attention.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe
+
+$(OUT)/libflash_attention.so: $(CSRC)/fa_api.cu $(HDRS)
+	@mkdir -p $(OUT)
+	$(NVCC) $(NVFLAGS) -shared -o $@ $< 2> $(OUT)/ptxas_fa_api.log || (cat $(OUT)/ptxas_fa_api.log; false)
+	@grep -E "error|spill" $(OUT)/ptxas_fa_api.log | sort | uniq -c | head -20 || true
+
+# the CPU oracle (test infrastructure, never linked into the product library)
+$(OUT)/liboracle.so: oracle/vanilla_attention.c
+	@mkdir -p $(OUT)
+	$(CC) -O2 -fPIC -shared -Wall -Wextra -o $@ $< -lm
+
+$(OUT)/tests: tests/cuda/test_flash_attention.cu oracle/vanilla_attention.c $(OUT)/libflash_attention.so
+	$(CC) -O2 -c -o $(OUT)/vanilla_attention.o oracle/vanilla_attention.c
+	$(NVCC) -std=c++17 -O2 $(ARCH) -Iinclude -o $@ tests/cuda/test_flash_attention.cu $(OUT)/vanilla_attention.o \
+	    -L$(OUT) -lflash_attention -Xlinker -rpath -Xlinker '$$ORIGIN'
+
+$(OUT)/umma_probe: tests/cuda/umma_probe.cu $(CSRC)/sm100_ptx.cuh
+	@mkdir -p $(OUT)
+	$(NVCC) -std=c++17 -O2 -lineinfo $(ARCH) -o $@ $<
+
+clean:
+	rm -rf $(OUT)
+
+.PHONY: all clean

@@ -1,0 +1,306 @@
+// fa_api.cu -- the extern "C" boundary of libflash_attention.so (see include/fa_b200.h).
+// Replaces the popart plugin glue of the reference (Op/GradOp/Opx/GradOpx/OpCreator,
+// flash_attention_ipu/cpp/flash_attention_qkv_packed.cpp:514-676): argument checking, shape
+// rules (:571-577, :530), kernel selection and launch.  No device allocation, no sync.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/fa_b200.h"
+#include "fa_fwd_sm100.cuh"
+#include "fa_generic.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+int fail(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define FA_CUDA_OK(expr)                                                                  \
+  do {                                                                                    \
+    cudaError_t e__ = (expr);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(FA_B200_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__));     \
+  } while (0)
+
+int launched() {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(FA_B200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+size_t elem_size(int dtype) { return dtype == FA_B200_F32 ? 4 : 2; }
+
+int check_problem(const fa_b200_problem *p) {
+  if (!p) return fail(FA_B200_ERR_INVALID, "null problem");
+  if (p->B <= 0 || p->H <= 0 || p->Lq <= 0 || p->Lk <= 0 || p->D <= 0)
+    return fail(FA_B200_ERR_INVALID, "non-positive dimension (B=%d H=%d Lq=%d Lk=%d D=%d)", p->B,
+                p->H, p->Lq, p->Lk, p->D);
+  if (p->dtype < FA_B200_F16 || p->dtype > FA_B200_F32)
+    return fail(FA_B200_ERR_UNSUPPORTED, "unknown dtype %d", p->dtype);
+  if (!(p->softmax_scale > 0.f)) return fail(FA_B200_ERR_INVALID, "softmax_scale must be > 0");
+  if (p->D > fa::kGenMaxD && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
+    return fail(FA_B200_ERR_UNSUPPORTED, "head dim %d > %d", p->D, fa::kGenMaxD);
+  return 0;
+}
+
+int check_tensor(const fa_b200_tensor *t, const char *name) {
+  if (!t || !t->ptr) return fail(FA_B200_ERR_INVALID, "null tensor %s", name);
+  return 0;
+}
+
+// the tensor path needs 16-byte aligned base + strides (TMA) and D in {64,128}
+bool tma_ok(const fa_b200_tensor *t, size_t es) {
+  return (reinterpret_cast<uintptr_t>(t->ptr) % 16 == 0) && (t->stride_l * es) % 16 == 0 &&
+         (t->stride_h * es) % 16 == 0 && (t->stride_b * es) % 16 == 0 && t->stride_l > 0;
+}
+
+int family(const fa_b200_problem *p) {
+  if (p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)) return 1;
+  if (p->D <= fa::kGenMaxD) return 0;
+  return FA_B200_ERR_UNSUPPORTED;
+}
+
+// ---------------------------------------------------------------- TMA descriptors
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void *sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      sym = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(sym);
+  }();
+  return fn;
+}
+
+// (B,H,L,D) tensor, box = 128 bytes of D x `box_rows` rows, 128B swizzle.
+int make_tmap(CUtensorMap *m, const fa_b200_tensor *t, int dtype, int B, int H, int L, int D,
+              int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return fail(FA_B200_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  const size_t es = elem_size(dtype);
+  CUtensorMapDataType dt = dtype == FA_B200_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                           : dtype == FA_B200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                   : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)L, (cuuint64_t)H, (cuuint64_t)B};
+  // a size-1 dimension's stride is never used for addressing but must still be legal
+  cuuint64_t sl = t->stride_l * es, sh = t->stride_h * es, sb = t->stride_b * es;
+  if (H == 1 && (sh == 0 || sh % 16)) sh = sl * L;
+  if (B == 1 && (sb == 0 || sb % 16)) sb = sh * H;
+  cuuint64_t strides[3] = {sl, sh, sb};
+  cuuint32_t box[4] = {(cuuint32_t)(128 / es), (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, dt, 4, t->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(FA_B200_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  return 0;
+}
+
+template <typename T>
+fa::View<T> view(const fa_b200_tensor *t) {
+  return fa::View<T>{reinterpret_cast<T *>(t->ptr), t->stride_b, t->stride_h, t->stride_l};
+}
+
+fa::GenericParams gparams(const fa_b200_problem *p) {
+  return fa::GenericParams{p->B, p->H, p->Lq, p->Lk, p->D, p->causal, p->q_pos0 - p->kv_pos0,
+                           p->softmax_scale};
+}
+
+unsigned blocks_for(int64_t rows, int per_block) { return (unsigned)((rows + per_block - 1) / per_block); }
+
+// ---------------------------------------------------------------- generic family
+template <typename T>
+int generic_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  const int64_t rows = (int64_t)p->B * p->H * p->Lq;
+  fa::fa_generic_fwd_kernel<T><<<blocks_for(rows, fa::kGenWarps), fa::kGenWarps * 32,
+                                 fa::kGenWarps * p->D * sizeof(float), st>>>(
+      view<const T>(q), view<const T>(k), view<const T>(v), view<T>(o), lse, gparams(p));
+  return launched();
+}
+
+template <typename T>
+int launch_delta(const fa_b200_problem *p, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                 float *delta, cudaStream_t st) {
+  const int64_t rows = (int64_t)p->B * p->H * p->Lq;
+  fa::fa_delta_kernel<T><<<blocks_for(rows, 4), 128, 0, st>>>(view<const T>(o), view<const T>(dout),
+                                                             delta, p->B, p->H, p->Lq, p->D);
+  return launched();
+}
+
+template <typename T>
+int generic_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+                const fa_b200_tensor *dv, float *delta, cudaStream_t st) {
+  if (int rc = launch_delta<T>(p, o, dout, delta, st)) return rc;
+  const int64_t qrows = (int64_t)p->B * p->H * p->Lq, krows = (int64_t)p->B * p->H * p->Lk;
+  const size_t sm = fa::kGenWarps * 2 * p->D * sizeof(float);
+  fa::fa_generic_bwd_dq_kernel<T><<<blocks_for(qrows, fa::kGenWarps), fa::kGenWarps * 32, sm, st>>>(
+      view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
+      view<T>(dq), gparams(p));
+  if (int rc = launched()) return rc;
+  fa::fa_generic_bwd_dkv_kernel<T><<<blocks_for(krows, fa::kGenWarps), fa::kGenWarps * 32, sm, st>>>(
+      view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
+      view<T>(dk), view<T>(dv), gparams(p));
+  return launched();
+}
+
+// ---------------------------------------------------------------- tensor family: forward
+template <int D, bool kBf16>
+int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+               const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  CUtensorMap tq, tk, tv, to;
+  if (int rc = make_tmap(&tq, q, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
+  if (int rc = make_tmap(&tk, k, p->dtype, p->B, p->H, p->Lk, D, fa::kBlockN)) return rc;
+  if (int rc = make_tmap(&tv, v, p->dtype, p->B, p->H, p->Lk, D, fa::kBlockN)) return rc;
+  if (int rc = make_tmap(&to, o, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
+  fa::FwdParams fp;
+  fp.lse = lse;
+  fp.Lq = p->Lq; fp.Lk = p->Lk; fp.H = p->H;
+  fp.causal = p->causal;
+  fp.shift = p->q_pos0 - p->kv_pos0;
+  fp.scale_log2 = p->softmax_scale * fa::kLog2e;
+  fp.num_pairs = (p->Lq + 2 * fa::kBlockM - 1) / (2 * fa::kBlockM);
+  auto kern = fa::fa_fwd_sm100_kernel<D, kBf16>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    FA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    fa::FwdSmem<D>::kAlloc));
+    attr_set = true;
+  }
+  const unsigned grid = (unsigned)((int64_t)p->B * p->H * fp.num_pairs);
+  kern<<<grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st>>>(tq, tk, tv, to, fp);
+  return launched();
+}
+
+}  // namespace
+
+// ================================================================== extern "C"
+extern "C" {
+
+const char *fa_b200_last_error(void) { return g_err; }
+int fa_b200_version(void) { return 100; }
+int64_t fa_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int fa_b200_kernel_family(const fa_b200_problem *p) {
+  if (int rc = check_problem(p)) return rc;
+  return family(p);
+}
+
+int fa_b200_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, void *stream) {
+  if (int rc = check_problem(p)) return rc;
+  if (check_tensor(q, "q") || check_tensor(k, "k") || check_tensor(v, "v") || check_tensor(o, "o"))
+    return FA_B200_ERR_INVALID;
+  if (!lse) return fail(FA_B200_ERR_INVALID, "null lse");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int fam = family(p);
+  const size_t es = elem_size(p->dtype);
+  if (fam == 1 && !(tma_ok(q, es) && tma_ok(k, es) && tma_ok(v, es) && tma_ok(o, es)))
+    return fail(FA_B200_ERR_INVALID,
+                "tensor path needs 16-byte aligned pointers and strides (TMA requirement)");
+  if (fam == 1) {
+    if (p->dtype == FA_B200_BF16)
+      return p->D == 128 ? tensor_fwd<128, true>(p, q, k, v, o, lse, st)
+                         : tensor_fwd<64, true>(p, q, k, v, o, lse, st);
+    return p->D == 128 ? tensor_fwd<128, false>(p, q, k, v, o, lse, st)
+                       : tensor_fwd<64, false>(p, q, k, v, o, lse, st);
+  }
+  if (fam == 0) {
+    switch (p->dtype) {
+      case FA_B200_F32: return generic_fwd<float>(p, q, k, v, o, lse, st);
+      case FA_B200_F16: return generic_fwd<__half>(p, q, k, v, o, lse, st);
+      default: return generic_fwd<__nv_bfloat16>(p, q, k, v, o, lse, st);
+    }
+  }
+  return fail(FA_B200_ERR_UNSUPPORTED, "no kernel for dtype %d, D=%d", p->dtype, p->D);
+}
+
+size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p) {
+  if (!p || p->B <= 0 || p->H <= 0 || p->Lq <= 0 || p->D <= 0) return 0;
+  const size_t rows = (size_t)p->B * p->H * p->Lq;
+  size_t bytes = ((rows * sizeof(float) + 255) / 256) * 256;  // delta[G][Lq]
+  if (family(p) == 1) bytes += rows * p->D * sizeof(float);   // fp32 dQ accumulator
+  return bytes;
+}
+
+int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+                const fa_b200_tensor *dv, void *workspace, size_t workspace_bytes, void *stream) {
+  if (int rc = check_problem(p)) return rc;
+  if (check_tensor(q, "q") || check_tensor(k, "k") || check_tensor(v, "v") || check_tensor(o, "o") ||
+      check_tensor(dout, "dout") || check_tensor(dq, "dq") || check_tensor(dk, "dk") ||
+      check_tensor(dv, "dv"))
+    return FA_B200_ERR_INVALID;
+  if (!lse) return fail(FA_B200_ERR_INVALID, "null lse");
+  if (!workspace || workspace_bytes < fa_b200_bwd_workspace_bytes(p))
+    return fail(FA_B200_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes,
+                fa_b200_bwd_workspace_bytes(p));
+  if (reinterpret_cast<uintptr_t>(workspace) % 256)
+    return fail(FA_B200_ERR_INVALID, "workspace must be 256-byte aligned");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  float *delta = reinterpret_cast<float *>(workspace);
+  int fam = family(p);
+  if (fam == 1) {
+    const size_t es = elem_size(p->dtype);
+    if (!(tma_ok(q, es) && tma_ok(k, es) && tma_ok(v, es) && tma_ok(dout, es) && tma_ok(dq, es) &&
+          tma_ok(dk, es) && tma_ok(dv, es)))
+      return fail(FA_B200_ERR_INVALID,
+                  "tensor path needs 16-byte aligned pointers and strides (TMA requirement)");
+    const size_t rows = (size_t)p->B * p->H * p->Lq;
+    float *dq_acc = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(workspace) +
+                                              ((rows * sizeof(float) + 255) / 256) * 256);
+    (void)dq_acc;  // TODO(bwd): tcgen05 backward; until then the SIMT kernels serve 16-bit too
+    fam = 0;
+  }
+  if (fam == 0) {
+    switch (p->dtype) {
+      case FA_B200_F32: return generic_bwd<float>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
+      case FA_B200_F16: return generic_bwd<__half>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
+      default: return generic_bwd<__nv_bfloat16>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
+    }
+  }
+  return fail(FA_B200_ERR_UNSUPPORTED, "no kernel for dtype %d, D=%d", p->dtype, p->D);
+}
+
+int fa_b200_merge(void *o_a, float *lse_a, const void *o_b, const float *lse_b, int64_t rows,
+                  int32_t D, int32_t dtype, void *stream) {
+  if (!o_a || !lse_a || !o_b || !lse_b || rows <= 0 || D <= 0)
+    return fail(FA_B200_ERR_INVALID, "bad merge arguments");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const unsigned grid = blocks_for(rows, 4);
+  switch (dtype) {
+    case FA_B200_F32:
+      fa::fa_merge_kernel<float><<<grid, 128, 0, st>>>((float *)o_a, lse_a, (const float *)o_b, lse_b, rows, D);
+      break;
+    case FA_B200_F16:
+      fa::fa_merge_kernel<__half><<<grid, 128, 0, st>>>((__half *)o_a, lse_a, (const __half *)o_b, lse_b, rows, D);
+      break;
+    case FA_B200_BF16:
+      fa::fa_merge_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((__nv_bfloat16 *)o_a, lse_a, (const __nv_bfloat16 *)o_b, lse_b, rows, D);
+      break;
+    default:
+      return fail(FA_B200_ERR_UNSUPPORTED, "unknown dtype %d", dtype);
+  }
+  return launched();
+}
+
+}  // extern "C"

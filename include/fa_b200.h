@@ -1,0 +1,103 @@
+/* fa_b200.h -- C ABI of libflash_attention.so (B200 / sm_100a).
+ *
+ * This is the drop-in boundary.  The reference loads a plugin of the same file name,
+ * build/libflash_attention.so, with ctypes (flash_attention_ipu/__init__.py:4-20) and
+ * the plugin's static initialisers register the popart op
+ * ("ai.graphcore","FlashAttentionQKVPacked",1) and its grad
+ * (flash_attention_ipu/cpp/flash_attention_qkv_packed.cpp:516-517, :618-625, :675-676).
+ * Here the same library instead exports plain C entry points that the Python side
+ * binds with ctypes and wraps as a torch.library op.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative fa_b200_status otherwise;
+ *    fa_b200_last_error() gives a thread-local message for the last failure.
+ *  - the library never allocates or frees device memory, never synchronises the
+ *    device and only enqueues work on the stream it is given (cudaStream_t as void*).
+ *  - the caller makes the tensors' device current before the call.
+ *  - tensors are 4-D (B, H, L, D) with D contiguous; strides are in ELEMENTS.
+ *    The packed (3,G,L,D) layout of the reference API is B=1, H=G,
+ *    q/k/v = base + {0,1,2}*G*L*D (zero copy).
+ */
+#ifndef FA_B200_H_
+#define FA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  FA_B200_OK = 0,
+  FA_B200_ERR_INVALID = -1,     /* bad argument (shape, stride, alignment, null pointer) */
+  FA_B200_ERR_UNSUPPORTED = -2, /* dtype / head-dim combination with no kernel           */
+  FA_B200_ERR_CUDA = -3,        /* a CUDA runtime / driver call failed                   */
+  FA_B200_ERR_WORKSPACE = -4    /* workspace too small                                   */
+} fa_b200_status;
+
+/* element types; matches FLOAT16 / FLOAT of the reference op definition
+ * (cpp/flash_attention_qkv_packed.cpp:609) plus bf16, which the IPU lacks. */
+typedef enum { FA_B200_F16 = 0, FA_B200_BF16 = 1, FA_B200_F32 = 2 } fa_b200_dtype;
+
+/* one (B,H,L,D) operand: device pointer + element strides (stride of D is 1). */
+typedef struct {
+  void *ptr;
+  int64_t stride_b, stride_h, stride_l;
+} fa_b200_tensor;
+
+/* problem description shared by forward and backward. */
+typedef struct {
+  int32_t B, H;          /* G = B*H independent attention groups                          */
+  int32_t Lq, Lk, D;     /* query rows, key/value rows, head dim                          */
+  int32_t dtype;         /* fa_b200_dtype of q,k,v,o,do,dq,dk,dv                          */
+  int32_t causal;        /* 1: key c visible to query r iff kv_pos0+c <= q_pos0+r         */
+  float softmax_scale;   /* S = scale * q.k ; the packed reference API uses 1.0           */
+  int32_t block_q_hint;  /* L/num_chunks_q  of the reference API: a tile-size HINT only   */
+  int32_t block_kv_hint; /* L/num_chunks_kv (cpp/flash_attention_qkv_packed.cpp:194-195)  */
+  int32_t q_pos0, kv_pos0; /* global sequence position of q row 0 / kv row 0 (ring steps) */
+} fa_b200_problem;
+
+/* Forward: replaces flashAttentionQKVPackedWithStash
+ * (cpp/flash_attention_qkv_packed.cpp:175-334; declared .hpp:15-24).
+ * o: (B,H,Lq,D) in `dtype`; lse: fp32 contiguous [B*H][Lq], natural-log logsumexp of
+ * the scaled, masked scores (the `logSumExp` stash, .hpp:10-13).  Rows with no visible
+ * key get o = 0, lse = -inf. */
+int fa_b200_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, void *stream);
+
+/* Backward: replaces flashAttentionQKVPackedGrad
+ * (cpp/flash_attention_qkv_packed.cpp:348-512; declared .hpp:31-38), except that O and
+ * LSE saved by the forward are consumed instead of re-running the forward (:357-359).
+ * workspace: device scratch of at least fa_b200_bwd_workspace_bytes(p) bytes,
+ * 256-byte aligned; contents need not be initialised. */
+int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+                const fa_b200_tensor *dv, void *workspace, size_t workspace_bytes,
+                void *stream);
+
+size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p);
+
+/* LSE merge of two partial results over disjoint key sets (ring-attention hop):
+ *   lse = logaddexp(lse_a, lse_b);  o = o_a*exp(lse_a-lse) + o_b*exp(lse_b-lse)
+ * written in place into (o_a, lse_a).  rows = B*H*Lq, o_* contiguous [rows][D].
+ * No reference counterpart (the reference is single-device). */
+int fa_b200_merge(void *o_a, float *lse_a, const void *o_b, const float *lse_b, int64_t rows,
+                  int32_t D, int32_t dtype, void *stream);
+
+/* Which kernel family a problem dispatches to: 1 = tcgen05/TMA sm_100a kernels,
+ * 0 = generic SIMT kernels (fp32 inputs / head dims the tensor path does not cover),
+ * negative = unsupported. */
+int fa_b200_kernel_family(const fa_b200_problem *p);
+
+/* Number of kernel launches the library has enqueued since load (all threads). */
+int64_t fa_b200_launch_count(void);
+
+const char *fa_b200_last_error(void);
+int fa_b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FA_B200_H_ */
