@@ -1,0 +1,133 @@
+"""ctypes binding of the C ABI declared in ``include/fa_b200.h``.
+
+This is the only place Python touches the native library.  Tensors cross the boundary as raw
+device pointers + element strides; the stream is torch's current CUDA stream.  Errors come back
+as negative status codes and are raised as ``RuntimeError`` with ``fa_b200_last_error()``.
+"""
+import ctypes
+from ctypes import POINTER, Structure, byref, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
+
+import torch
+
+from .. import _lib, _lib_path  # loaded (or ImportError raised) by the package __init__
+
+FA_B200_F16, FA_B200_BF16, FA_B200_F32 = 0, 1, 2
+_DTYPES = {torch.float16: FA_B200_F16, torch.bfloat16: FA_B200_BF16, torch.float32: FA_B200_F32}
+
+EXPORTED_SYMBOLS = (
+    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_merge",
+    "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_last_error", "fa_b200_version",
+)
+
+
+class Tensor(Structure):  # fa_b200_tensor
+    _fields_ = [("ptr", c_void_p), ("stride_b", c_int64), ("stride_h", c_int64), ("stride_l", c_int64)]
+
+
+class Problem(Structure):  # fa_b200_problem
+    _fields_ = [
+        ("B", c_int32), ("H", c_int32), ("Lq", c_int32), ("Lk", c_int32), ("D", c_int32),
+        ("dtype", c_int32), ("causal", c_int32), ("softmax_scale", c_float),
+        ("block_q_hint", c_int32), ("block_kv_hint", c_int32), ("q_pos0", c_int32), ("kv_pos0", c_int32),
+    ]
+
+
+_PT, _PP = POINTER(Tensor), POINTER(Problem)
+_lib.fa_b200_fwd.argtypes = [_PP, _PT, _PT, _PT, _PT, c_void_p, c_void_p]
+_lib.fa_b200_fwd.restype = c_int
+_lib.fa_b200_bwd.argtypes = [_PP, _PT, _PT, _PT, _PT, _PT, c_void_p, _PT, _PT, _PT, c_void_p, c_size_t, c_void_p]
+_lib.fa_b200_bwd.restype = c_int
+_lib.fa_b200_bwd_workspace_bytes.argtypes = [_PP]
+_lib.fa_b200_bwd_workspace_bytes.restype = c_size_t
+_lib.fa_b200_merge.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]
+_lib.fa_b200_merge.restype = c_int
+_lib.fa_b200_kernel_family.argtypes = [_PP]
+_lib.fa_b200_kernel_family.restype = c_int
+_lib.fa_b200_launch_count.argtypes = []
+_lib.fa_b200_launch_count.restype = c_int64
+_lib.fa_b200_last_error.argtypes = []
+_lib.fa_b200_last_error.restype = c_char_p
+_lib.fa_b200_version.argtypes = []
+_lib.fa_b200_version.restype = c_int
+
+
+def library_path() -> str:
+    return _lib_path
+
+
+def launch_count() -> int:
+    return int(_lib.fa_b200_launch_count())
+
+
+def version() -> int:
+    return int(_lib.fa_b200_version())
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = _lib.fa_b200_last_error().decode(errors="replace")
+        raise RuntimeError(f"{what} failed (status {rc}): {msg}")
+
+
+def _tensor(t: torch.Tensor) -> Tensor:
+    # t is (B, H, L, D) with stride(-1) == 1
+    return Tensor(t.data_ptr(), t.stride(0), t.stride(1), t.stride(2))
+
+
+def _require_cuda(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if not t.is_cuda:
+            raise RuntimeError(
+                "flash_attention_ipu_b200 runs on CUDA (sm_100a) tensors only; there is no CPU path"
+            )
+
+
+def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
+                 block_q: int = 0, block_kv: int = 0, q_pos0: int = 0, kv_pos0: int = 0) -> Problem:
+    if q.dtype not in _DTYPES:
+        raise RuntimeError(f"unsupported dtype {q.dtype}")
+    B, H, Lq, D = q.shape
+    return Problem(B, H, Lq, k.shape[2], D, _DTYPES[q.dtype], int(bool(causal)), float(scale),
+                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0))
+
+
+def kernel_family(prob: Problem) -> int:
+    return int(_lib.fa_b200_kernel_family(byref(prob)))
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def fwd(prob: Problem, q, k, v, o, lse) -> None:
+    _require_cuda(q, k, v, o, lse)
+    with torch.cuda.device(q.device):
+        rc = _lib.fa_b200_fwd(byref(prob), byref(_tensor(q)), byref(_tensor(k)), byref(_tensor(v)),
+                              byref(_tensor(o)), lse.data_ptr(), _stream(q))
+    _check(rc, "fa_b200_fwd")
+
+
+def bwd_workspace_bytes(prob: Problem) -> int:
+    return int(_lib.fa_b200_bwd_workspace_bytes(byref(prob)))
+
+
+def bwd(prob: Problem, q, k, v, o, dout, lse, dq, dk, dv, workspace) -> None:
+    _require_cuda(q, k, v, o, dout, lse, dq, dk, dv, workspace)
+    with torch.cuda.device(q.device):
+        rc = _lib.fa_b200_bwd(byref(prob), byref(_tensor(q)), byref(_tensor(k)), byref(_tensor(v)),
+                              byref(_tensor(o)), byref(_tensor(dout)), lse.data_ptr(),
+                              byref(_tensor(dq)), byref(_tensor(dk)), byref(_tensor(dv)),
+                              workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                              _stream(q))
+    _check(rc, "fa_b200_bwd")
+
+
+def merge(o_a, lse_a, o_b, lse_b) -> None:
+    """In-place LSE merge of two partial attention results (ring hop)."""
+    _require_cuda(o_a, lse_a, o_b, lse_b)
+    D = o_a.shape[-1]
+    rows = o_a.numel() // D
+    with torch.cuda.device(o_a.device):
+        rc = _lib.fa_b200_merge(o_a.data_ptr(), lse_a.data_ptr(), o_b.data_ptr(), lse_b.data_ptr(),
+                                rows, D, _DTYPES[o_a.dtype], _stream(o_a))
+    _check(rc, "fa_b200_merge")

@@ -142,15 +142,15 @@ int main(int argc, char **argv) {
     for (auto &c : mid) run_case("ref-matrix", 2, 2048, 128, c[0], c[1], dt, 1, true, 1e-2, 1.0);
   // --- tensor-path shapes: single tile, tile pair, ragged tails, D=64, non-causal extension
   for (int dt : {FA_B200_BF16, FA_B200_F16}) {
-    run_case("tile", 1, 128, 128, 1, 1, dt, 0, true, 1e-2, 5e-2);
-    run_case("tile", 1, 128, 128, 1, 1, dt, 1, true, 1e-2, 5e-2);
-    run_case("tile", 2, 256, 128, 1, 1, dt, 1, true, 1e-2, 5e-2);
-    run_case("tile", 2, 512, 64, 1, 1, dt, 1, true, 1e-2, 5e-2);
+    run_case("tile", 1, 128, 128, 1, 1, dt, 0, true, 1e-2, 1e-1);
+    run_case("tile", 1, 128, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
+    run_case("tile", 2, 256, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
+    run_case("tile", 2, 512, 64, 1, 1, dt, 1, true, 1e-2, 1e-1);
     run_case("tile", 3, 1024, 64, 4, 4, dt, 1, true, 1e-2, 1e-1);
-    run_case("tile", 2, 512, 64, 4, 2, dt, 0, true, 1e-2, 5e-2);
-    run_case("ragged", 2, 200, 128, 1, 1, dt, 1, true, 1e-2, 5e-2);
-    run_case("ragged", 2, 331, 64, 1, 1, dt, 0, true, 1e-2, 5e-2);
-    run_case("ragged", 1, 8, 128, 1, 1, dt, 1, true, 1e-2, 5e-2);
+    run_case("tile", 2, 512, 64, 4, 2, dt, 0, true, 1e-2, 1e-1);
+    run_case("ragged", 2, 200, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
+    run_case("ragged", 2, 331, 64, 1, 1, dt, 0, true, 1e-2, 1e-1);
+    run_case("ragged", 1, 8, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
   }
   printf("%d cases run, %d failed\n", g_run, g_failed);
   return g_failed;

@@ -1,0 +1,233 @@
+"""GPU parity tests (``-m gpu``): the CUDA path, called through the public API / C ABI, against
+the CPU oracle on the same seeded inputs and against the golden fixtures produced by the
+reference's own code.  Mirrors tests/python/test_flash_attention_qkv_packed.py:56-93 and
+tests/python/test_scaled_dot_product_attention.py:59-153 of the reference with device="cuda".
+
+Tolerances (stated here):
+  * fp32 inputs: atol 1e-3 / rtol 1e-5 -- the reference's own fp32 row (…_packed.py:78).
+  * 16-bit forward: max-abs <= 1e-2 against the fp32 oracle on the same rounded inputs.
+  * 16-bit gradients: max-abs no worse than the reference math evaluated in the same dtype on
+    the same inputs (north_star's second clause; bf16 cannot reach 1e-2 max-abs on N(0,1)
+    data even in torch's own kernels), never above the reference's accepted 1.0
+    (tests/cpp/test_flash_attention.cpp:292-295), plus a relative Frobenius bound of 1e-2.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, SEED, packed_inputs, sdpa_inputs
+from oracle import attention_oracle as ao
+
+pytestmark = pytest.mark.gpu
+DT = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}
+
+
+def _native_loaded():
+    from flash_attention_ipu_b200._impl import native
+    assert native.library_path().endswith("libflash_attention.so")
+    return native
+
+
+def run_packed(qkv_cpu, grad_cpu, dtype, ncq=1, nckv=1, **kw):
+    import flash_attention_ipu as fa
+    x = qkv_cpu.to("cuda", dtype).requires_grad_(True)
+    out = fa.flash_attention_qkv_packed(x, ncq, nckv, **kw)
+    out.backward(grad_cpu.to("cuda", dtype))
+    torch.cuda.synchronize()
+    return out.detach().float().cpu(), x.grad.float().cpu()
+
+
+def rel_fro(a, b):
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def same_dtype_reference_error(qkv, grad, dtype, causal=True):
+    """max-abs error of the reference's math run in `dtype` on the CPU (per q/k/v gradient)."""
+    x = qkv.to(dtype).requires_grad_(True)
+    (ao.packed_attention_reference(x, causal) * grad.to(dtype)).sum().backward()
+    x32 = qkv.to(dtype).float().requires_grad_(True)
+    (ao.packed_attention_reference(x32, causal) * grad.to(dtype).float()).sum().backward()
+    return (x.grad.float() - x32.grad).abs().amax(dim=(1, 2, 3))
+
+
+@pytest.mark.parametrize("name,G,L,D", [("packed_g2_l256_d128", 2, 256, 128), ("packed_g3_l128_d64", 3, 128, 64),
+                                        ("packed_g4_l6_d2", 4, 6, 2)])
+@pytest.mark.parametrize("dtype", ["fp32", "bf16", "fp16"])
+def test_golden_fixtures(name, G, L, D, dtype):
+    """CUDA path vs outputs of the reference's own code (tests/golden, oracle/gen_golden.py)."""
+    _native_loaded()
+    gold = np.load(GOLDEN / f"{name}.npz")
+    qkv, grad = packed_inputs(G, L, D)
+    out, dqkv = run_packed(qkv, grad, DT[dtype])
+    gout, gd = torch.from_numpy(gold["out"]), torch.from_numpy(gold["dqkv"])
+    if dtype == "fp32":
+        torch.testing.assert_close(out, gout, atol=1e-3, rtol=1e-5)
+        torch.testing.assert_close(dqkv, gd, atol=1e-3, rtol=1e-5)
+    else:
+        # golden is for unrounded inputs: allow input-rounding noise on top (reference row: 1e-2/1e-2)
+        torch.testing.assert_close(out, gout, atol=3e-2, rtol=1e-2)
+        assert rel_fro(dqkv, gd) < 2e-2
+
+
+@pytest.mark.parametrize("L", [256, 1024, 4096])
+@pytest.mark.parametrize("dtype", ["bf16", "fp16", "fp32"])
+def test_packed_vs_oracle(L, dtype):
+    """reference matrix: N=4, D=128, chunks 16/16 (test_flash_attention_qkv_packed.py:56-76)."""
+    G, D = 4, 128
+    qkv, grad = packed_inputs(G, L, D)
+    qkv, grad = qkv.to(DT[dtype]).float(), grad.to(DT[dtype]).float()  # oracle sees the rounded inputs
+    out, dqkv = run_packed(qkv, grad, DT[dtype], 16, 16)
+    ref = ao.packed_attention_reference(qkv)
+    dref = ao.vanilla_attention_grad(grad, qkv)
+    if dtype == "fp32":
+        torch.testing.assert_close(out, ref, atol=1e-3, rtol=1e-5)
+        torch.testing.assert_close(dqkv, dref, atol=1e-3, rtol=1e-5)
+        return
+    assert (out - ref).abs().max().item() <= 1e-2
+    err = (dqkv - dref).abs().amax(dim=(1, 2, 3))
+    bound = torch.maximum(same_dtype_reference_error(qkv, grad, DT[dtype]), torch.tensor(1e-2))
+    assert (err <= bound).all() and (err <= 1.0).all(), (err, bound)
+    for t in range(3):
+        assert rel_fro(dqkv[t], dref[t]) < 1e-2
+
+
+@pytest.mark.parametrize("dtype", ["bf16", "fp16"])
+def test_packed_long_sequence(dtype):
+    """L=16384 row of the reference matrix (G reduced to 1 so the CPU oracle stays in seconds);
+    oracle = the blocked restatement of the chunked algorithm."""
+    G, L, D = 1, 16384, 128
+    qkv, grad = packed_inputs(G, L, D)
+    qkv, grad = qkv.to(DT[dtype]).float(), grad.to(DT[dtype]).float()
+    out, dqkv = run_packed(qkv, grad, DT[dtype], 16, 16)
+    ref, _ = ao.chunked_attention_forward(qkv, 16, 16)
+    dref = ao.chunked_attention_backward(grad, qkv, 16, 16)
+    assert (out - ref).abs().max().item() <= 1e-2
+    for t in range(3):
+        assert rel_fro(dqkv[t], dref[t]) < 1e-2
+        assert (dqkv[t] - dref[t]).abs().max().item() <= 1.0
+
+
+@pytest.mark.parametrize("dtype", ["bf16", "fp32"])
+def test_chunk_hints_do_not_change_the_result(dtype):
+    """tests/cpp/test_flash_attention.cpp:245-259: every chunking gives the same answer."""
+    qkv, grad = packed_inputs(2, 512, 64)
+    base = run_packed(qkv, grad, DT[dtype], 1, 1)
+    for ncq, nckv in [(2, 2), (4, 2), (2, 4), (8, 8), (512, 256)]:
+        got = run_packed(qkv, grad, DT[dtype], ncq, nckv)
+        assert torch.equal(got[0], base[0])
+        assert rel_fro(got[1], base[1]) < 1e-5  # dQ accumulates by atomics: order may differ
+
+
+@pytest.mark.parametrize("G,L,D", [(2, 200, 128), (1, 8, 64), (3, 331, 64), (1, 129, 128), (2, 1, 64)])
+@pytest.mark.parametrize("causal", [True, False])
+def test_ragged_lengths_and_noncausal(G, L, D, causal):
+    """edge cases: lengths that are not tile multiples, single row, non-causal extension (unpinned)."""
+    qkv, grad = packed_inputs(G, L, D)
+    qkv, grad = qkv.bfloat16().float(), grad.bfloat16().float()
+    out, dqkv = run_packed(qkv, grad, torch.bfloat16, causal=causal)
+    ref = ao.packed_attention_reference(qkv, causal)
+    dref = ao.vanilla_attention_grad(grad, qkv, causal)
+    assert (out - ref).abs().max().item() <= 1e-2
+    assert rel_fro(dqkv, dref) < 1e-2
+
+
+def test_causality_property_full_size():
+    """size-independent property at a BASELINE config-3 slice (T=8192, d=128): the first n rows
+    of the output depend only on the first n rows of q, k, v."""
+    import flash_attention_ipu as fa
+    torch.manual_seed(SEED)
+    qkv = torch.randn(3, 2, 8192, 128, device="cuda", dtype=torch.bfloat16)
+    qkv[0] *= 128 ** -0.5
+    full = fa.flash_attention_qkv_packed(qkv, 8, 8)
+    for n in (128, 1000, 4096):
+        part = fa.flash_attention_qkv_packed(qkv[:, :, :n].contiguous(), 1, 1)
+        assert torch.equal(part, full[:, :n])
+    # row 0 attends only to key 0 -> out[0] == v[0]
+    assert torch.equal(full[:, 0], qkv[2][:, 0])
+    # linearity in v: attn(q, k, 2v) == 2 attn(q, k, v) exactly (power-of-two scaling)
+    qkv2 = qkv.clone(); qkv2[2] *= 2
+    assert torch.equal(fa.flash_attention_qkv_packed(qkv2, 8, 8), 2 * full)
+
+
+@pytest.mark.parametrize("batch", [(2,), (2, 3), (2, 3, 5)])
+@pytest.mark.parametrize("L", [256, 1024])
+@pytest.mark.parametrize("dtype", ["fp32", "fp16", "bf16"])
+def test_sdpa_override(batch, L, dtype):
+    """tests/python/test_scaled_dot_product_attention.py:59-113: patched SDPA on the device vs
+    torch CPU SDPA, out and grad_q/k/v."""
+    import torch.nn.functional as F
+    import flash_attention_ipu_b200._impl.scaled_dot_product_attention as mod
+    native = _native_loaded()
+    qkv, grad = sdpa_inputs(batch, L, 64)
+    qkv, grad = qkv.to(DT[dtype]).float(), grad.to(DT[dtype]).float()
+    xr = qkv.clone().requires_grad_(True)
+    ref = ao.sdpa_reference(xr[0], xr[1], xr[2])
+    (ref * grad).sum().backward()
+    mod.install()
+    try:
+        before = native.launch_count()
+        x = qkv.to("cuda", DT[dtype]).requires_grad_(True)
+        out = F.scaled_dot_product_attention(x[0], x[1], x[2], is_causal=True)
+        out.backward(grad.to("cuda", DT[dtype]))
+        torch.cuda.synchronize()
+        assert native.launch_count() > before  # the native kernels ran, not torch's
+    finally:
+        mod.uninstall()
+    out, g = out.detach().float().cpu(), x.grad.float().cpu()
+    assert out.shape == ref.shape
+    if dtype == "fp32":
+        torch.testing.assert_close(out, ref.detach(), atol=1e-3, rtol=1e-5)
+        torch.testing.assert_close(g, xr.grad, atol=1e-3, rtol=1e-5)
+    else:
+        assert (out - ref.detach()).abs().max().item() <= 1e-2
+        assert rel_fro(g, xr.grad) < 1e-2
+
+
+def test_sdpa_strided_nanogpt_layout():
+    """q, k, v as nanoGPT makes them (demo/nanoGPT/model.py:56-59): (B,T,3C) split, viewed
+    (B,T,nh,hs) and transposed -- consumed in place through their strides."""
+    from flash_attention_ipu_b200._impl import ops
+    B, T, nh, hs = 2, 256, 6, 64
+    torch.manual_seed(SEED)
+    c_attn = torch.randn(B, T, 3 * nh * hs, device="cuda", dtype=torch.bfloat16)
+    q, k, v = (t.view(B, T, nh, hs).transpose(1, 2) for t in c_attn.split(nh * hs, dim=2))
+    out, lse = ops.attention_fwd(q, k, v, hs ** -0.5, True, 128, 128)
+    ref = ao.sdpa_reference(q.float().cpu(), k.float().cpu(), v.float().cpu())
+    assert (out.float().cpu() - ref).abs().max().item() <= 1e-2
+    assert out.stride() == q.contiguous().transpose(1, 2).contiguous().transpose(1, 2).stride() or out.stride(-1) == 1
+
+
+def test_memory_is_linear_in_sequence_length():
+    """The reference's reason to exist (README.md:59-73; the OOM test at
+    tests/python/test_scaled_dot_product_attention.py:116-153): no L x L tensor is materialised."""
+    import flash_attention_ipu as fa
+    G, L, D = 16, 16384, 64
+    qkv = torch.randn(3, G, L, D, device="cuda", dtype=torch.bfloat16).requires_grad_(True)
+    torch.cuda.synchronize(); torch.cuda.reset_peak_memory_stats()
+    base = torch.cuda.memory_allocated()
+    out = fa.flash_attention_qkv_packed(qkv, 16, 16)
+    out.sum().backward()
+    torch.cuda.synchronize()
+    extra = torch.cuda.max_memory_allocated() - base
+    scores_bytes = G * L * L * 2
+    assert extra < 8 * qkv.numel() * 2, extra       # O(L): a few copies of qkv (+ fp32 dQ scratch)
+    assert extra < scores_bytes / 20
+
+
+def test_merge_kernel():
+    native = _native_loaded()
+    torch.manual_seed(3)
+    o_a = torch.randn(4, 100, 64, device="cuda").bfloat16(); o_b = torch.randn_like(o_a)
+    lse_a = torch.randn(4, 100, device="cuda"); lse_b = torch.randn(4, 100, device="cuda")
+    lse_b[0, :10] = float("-inf")
+    ro, rl = ao.merge_partials(o_a.float().cpu(), lse_a.cpu(), o_b.float().cpu(), lse_b.cpu())
+    native.merge(o_a, lse_a, o_b, lse_b)
+    assert (o_a.float().cpu() - ro).abs().max().item() < 2e-2
+    assert (lse_a.cpu() - rl).abs().max().item() < 1e-5
+
+
+def test_errors_are_loud():
+    native = _native_loaded()
+    q = torch.zeros(1, 1, 128, 512, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="fa_b200_fwd failed"):
+        native.fwd(native.make_problem(q, q, True, 1.0), q, q, q, q, torch.zeros(1, 1, 128, device="cuda"))
