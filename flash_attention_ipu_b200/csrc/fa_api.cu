@@ -6,8 +6,10 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <type_traits>
 
 #include "../../include/fa_b200.h"
+#include "fa_bwd_sm100.cuh"
 #include "fa_fwd_sm100.cuh"
 #include "fa_generic.cuh"
 
@@ -190,6 +192,64 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   return launched();
 }
 
+// ---------------------------------------------------------------- tensor family: backward
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+int lq_pad(const fa_b200_problem *p) { return (p->Lq + 127) / 128 * 128; }
+// workspace: delta[G][Lq_pad] | lse2[G][Lq_pad] | dq_acc[G][Lq][D] (fp32), each 256-byte aligned
+size_t ws_stat_bytes(const fa_b200_problem *p) {
+  return align256((size_t)p->B * p->H * lq_pad(p) * sizeof(float));
+}
+
+template <int D, bool kBf16>
+int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+               const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+               const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+               const fa_b200_tensor *dv, void *workspace, cudaStream_t st) {
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  uint8_t *ws = reinterpret_cast<uint8_t *>(workspace);
+  float *delta = reinterpret_cast<float *>(ws);
+  float *lse2 = reinterpret_cast<float *>(ws + ws_stat_bytes(p));
+  float *dq_acc = reinterpret_cast<float *>(ws + 2 * ws_stat_bytes(p));
+  const int G = p->B * p->H, Lp = lq_pad(p);
+  const size_t acc_bytes = (size_t)G * p->Lq * D * sizeof(float);
+  FA_CUDA_OK(cudaMemsetAsync(dq_acc, 0, acc_bytes, st));
+  fa::fa_bwd_prep_kernel<T><<<blocks_for((int64_t)G * Lp, 4), 128, 0, st>>>(
+      reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
+      reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
+      delta, lse2, p->B, p->H, p->Lq, Lp, D);
+  if (int rc = launched()) return rc;
+
+  fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
+  CUtensorMap tq, tk, tv, tdo, tdq, tdk, tdv;
+  if (int rc = make_tmap(&tq, q, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
+  if (int rc = make_tmap(&tk, k, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
+  if (int rc = make_tmap(&tv, v, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
+  if (int rc = make_tmap(&tdo, dout, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
+  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 128)) return rc;
+  if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
+  if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
+  fa::BwdParams bp;
+  bp.lse2 = lse2; bp.delta = delta;
+  bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
+  bp.causal = p->causal; bp.shift = p->q_pos0 - p->kv_pos0;
+  bp.scale = p->softmax_scale; bp.scale_log2 = p->softmax_scale * fa::kLog2e;
+  bp.num_kv_tiles = (p->Lk + 127) / 128;
+  auto kern = fa::fa_bwd_sm100_kernel<D, kBf16>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    fa::BwdSmem<D>::kBytes));
+    attr_set = true;
+  }
+  const unsigned grid = (unsigned)((int64_t)G * bp.num_kv_tiles);
+  kern<<<grid, fa::kBwdThreads, fa::BwdSmem<D>::kBytes, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, bp);
+  if (int rc = launched()) return rc;
+  // dQ = softmax_scale * dq_acc, cast to the output dtype
+  fa::fa_convert_kernel<T><<<148 * 8, 256, 0, st>>>(dq_acc, view<T>(dq), p->B, p->H, p->Lq, D,
+                                                     p->softmax_scale);
+  return launched();
+}
+
 }  // namespace
 
 // ================================================================== extern "C"
@@ -235,10 +295,9 @@ int fa_b200_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 
 size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p) {
   if (!p || p->B <= 0 || p->H <= 0 || p->Lq <= 0 || p->D <= 0) return 0;
-  const size_t rows = (size_t)p->B * p->H * p->Lq;
-  size_t bytes = ((rows * sizeof(float) + 255) / 256) * 256;  // delta[G][Lq]
-  if (family(p) == 1) bytes += rows * p->D * sizeof(float);   // fp32 dQ accumulator
-  return bytes;
+  if (family(p) == 1)
+    return 2 * ws_stat_bytes(p) + align256((size_t)p->B * p->H * p->Lq * p->D * sizeof(float));
+  return align256((size_t)p->B * p->H * p->Lq * sizeof(float));  // delta[G][Lq]
 }
 
 int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
@@ -265,11 +324,11 @@ int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
           tma_ok(dk, es) && tma_ok(dv, es)))
       return fail(FA_B200_ERR_INVALID,
                   "tensor path needs 16-byte aligned pointers and strides (TMA requirement)");
-    const size_t rows = (size_t)p->B * p->H * p->Lq;
-    float *dq_acc = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(workspace) +
-                                              ((rows * sizeof(float) + 255) / 256) * 256);
-    (void)dq_acc;  // TODO(bwd): tcgen05 backward; until then the SIMT kernels serve 16-bit too
-    fam = 0;
+    if (p->dtype == FA_B200_BF16)
+      return p->D == 128 ? tensor_bwd<128, true>(p, q, k, v, o, dout, lse, dq, dk, dv, workspace, st)
+                         : tensor_bwd<64, true>(p, q, k, v, o, dout, lse, dq, dk, dv, workspace, st);
+    return p->D == 128 ? tensor_bwd<128, false>(p, q, k, v, o, dout, lse, dq, dk, dv, workspace, st)
+                       : tensor_bwd<64, false>(p, q, k, v, o, dout, lse, dq, dk, dv, workspace, st);
   }
   if (fam == 0) {
     switch (p->dtype) {

@@ -1,0 +1,417 @@
+// fa_bwd_sm100.cuh -- backward attention kernel for B200 (sm_100a).
+//
+// Replaces the backward graph of the reference, flashAttentionQKVPackedGrad
+// (flash_attention_ipu/cpp/flash_attention_qkv_packed.cpp:348-512).  Same loop order as the
+// reference -- KV tile outer / stationary, Q tiles inner (:410-497) -- and the same math:
+//   P = exp(S - LSE) (:457-459), dV += P^T dO (:462), dP = dO V^T (:465),
+//   dS = P o (dP - D) (:466-467), dQ += dS K (:470), dK += dS^T Q (:472),
+// but O/LSE come from the forward instead of a recompute (:357-359) and D = rowsum(O o dO)
+// (:374-377) from a small pre-kernel.  Everything is computed TRANSPOSED (keys on the TMEM
+// lanes) so that P^T and dS^T are directly the A operands of the dV and dK GEMMs:
+//
+//   S^T  = K_j Q_i^T      SS   A = K (K-major)      B = Q_i  (K-major)      -> TMEM S
+//   dP^T = V_j dO_i^T     SS   A = V (K-major)      B = dO_i (K-major)      -> TMEM dP
+//   dV  += P^T dO_i       TS   A = P^T (TMEM, bf16) B = dO_i (MN-major)     -> TMEM dV
+//   dQ_i = dS K_j         SS   A = dS^T smem (MN-major) B = K (MN-major)    -> TMEM dQ (aliases dP)
+//   dK  += dS^T Q_i       SS   A = dS^T smem (K-major)  B = Q_i (MN-major)  -> TMEM dK
+//
+// TMEM (512 cols, D=128): dK [0,128) dV [128,256) S/P^T [256,384) dP^T/dQ [384,512).
+// Issue order per Q tile:  dP(i) dV(i) S(i+1) dQ(i) dK(i)  -- the exp of tile i+1 and the drain of
+// dQ(i) both happen in the shadow of other GEMMs.  dQ tiles are accumulated across KV tiles in
+// an fp32 scratch by TMA reduce-add and cast afterwards.
+//
+//   warps 0-7  : compute (2 warpgroups; thread <-> key row; WG w owns query columns [64w,64w+64))
+//   warps 8-11 : dQ drain (TMEM -> regs -> smem -> TMA reduce-add)
+//   warp 12 TMA producer | warp 13 MMA issuer | warp 14 TMEM alloc | warp 15 idle
+#pragma once
+#include "fa_fwd_sm100.cuh"
+
+namespace fa {
+
+constexpr int kBwdThreads = 512;
+
+struct BwdParams {
+  const float *lse2;   // [G][Lq_pad]  lse * log2(e); +inf for padding / rows without keys
+  const float *delta;  // [G][Lq_pad]  rowsum(O o dO); 0 for padding
+  int Lq, Lk, H, Lq_pad;
+  int causal, shift;
+  float scale, scale_log2;
+  int num_kv_tiles;    // ceil(Lk / 128)
+};
+
+template <int D>
+struct BwdSmem {
+  static constexpr int kTileBytes = 128 * D * 2;
+  static constexpr int kHalfBytes = 128 * 128;
+  static constexpr int kKOff = 0;
+  static constexpr int kVOff = kKOff + kTileBytes;
+  static constexpr int kQOff = kVOff + kTileBytes;            // 2 stages (epilogue: dK | dV staging)
+  static constexpr int kDOOff = kQOff + 2 * kTileBytes;       // 1 stage
+  static constexpr int kDSOff = kDOOff + kTileBytes;          // dS^T [128 keys][128 q] bf16
+  static constexpr int kDQOff = kDSOff + 2 * kHalfBytes;      // fp32 staging [128 q][64 d]
+  static constexpr int kStatOff = kDQOff + 2 * kHalfBytes;    // 2 stages x (lse2[128] | delta[128])
+  static constexpr int kBarOff = kStatOff + 2 * 1024;
+  static constexpr int kNumBars = 16;
+  static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
+  static constexpr int kBytes = kTmemPtrOff + 16;
+};
+
+// first Q tile that sees any key of KV tile j
+__device__ __forceinline__ int bwd_first_q_tile(const BwdParams &p, int j) {
+  if (!p.causal) return 0;
+  const int a = j * 128 - p.shift;
+  return a <= 0 ? 0 : a / 128;
+}
+
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                    const __grid_constant__ CUtensorMap tmDQ, const __grid_constant__ CUtensorMap tmDK,
+                    const __grid_constant__ CUtensorMap tmDV, const BwdParams p) {
+  using L = BwdSmem<D>;
+  constexpr int kHalves = D / 64;
+  constexpr uint32_t kColDK = 0, kColDV = D, kColS = 2 * D, kColDP = 2 * D + 128;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
+  uint64_t *kv_full = bars + 0;
+  uint64_t *q_full = bars + 1;    // [2]
+  uint64_t *q_empty = bars + 3;   // [2]
+  uint64_t *do_full = bars + 5;
+  uint64_t *do_empty = bars + 6;
+  uint64_t *s_full = bars + 7;    // MMA -> compute : S^T(i) ready
+  uint64_t *p_full = bars + 8;    // compute -> MMA : P^T(i) in TMEM        (256 arrivals)
+  uint64_t *dp_full = bars + 9;   // MMA -> compute : dP^T(i) ready
+  uint64_t *ds_full = bars + 10;  // compute -> MMA : dS^T(i) in smem       (256 arrivals)
+  uint64_t *dq_full = bars + 11;  // MMA -> drain   : dQ(i) ready
+  uint64_t *dq_empty = bars + 12; // drain -> MMA   : dQ(i) left TMEM       (128 arrivals)
+  uint64_t *dkv_full = bars + 13; // MMA -> compute : final dK, dV ready
+  uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int g = blockIdx.x / p.num_kv_tiles;
+  const int j = blockIdx.x % p.num_kv_tiles;  // ascending: the KV tiles with most Q tiles first
+  const int b = g / p.H, h = g % p.H;
+  const int num_q_tiles = (p.Lq + 127) / 128;
+  const int i0 = bwd_first_q_tile(p, j);
+  const int n = max(num_q_tiles - i0, 0);
+
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) {
+    printf("fa_b200: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  if (warp == 12 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQ); tma_prefetch_desc(&tmDK); tma_prefetch_desc(&tmDV);
+  }
+  if (warp == 13 && lane == 0) {
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+    mbar_init(do_full, 1); mbar_init(do_empty, 1);
+    mbar_init(s_full, 1); mbar_init(p_full, 256); mbar_init(dp_full, 1); mbar_init(ds_full, 256);
+    mbar_init(dq_full, 1); mbar_init(dq_empty, 128); mbar_init(dkv_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 14) tmem_alloc<512>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 12) {
+    // ============================== TMA producer ==============================
+    reg_dealloc<40>();
+    if (lane == 0 && n > 0) {
+      mbar_arrive_expect_tx(kv_full, 2 * L::kTileBytes);
+      for (int hh = 0; hh < kHalves; ++hh) {
+        tma_load_4d(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
+        tma_load_4d(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
+      }
+      const float *lse_g = p.lse2 + static_cast<size_t>(g) * p.Lq_pad;
+      const float *delta_g = p.delta + static_cast<size_t>(g) * p.Lq_pad;
+      for (int it = 0; it < n; ++it) {
+        const int i = i0 + it, s = it & 1;
+        mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(&q_full[s], L::kTileBytes + 1024);
+        for (int hh = 0; hh < kHalves; ++hh)
+          tma_load_4d(&tmQ, &q_full[s], smem + L::kQOff + s * L::kTileBytes + hh * L::kHalfBytes,
+                      hh * 64, i * 128, h, b);
+        bulk_load_1d(smem + L::kStatOff + s * 1024, lse_g + i * 128, 512, &q_full[s]);
+        bulk_load_1d(smem + L::kStatOff + s * 1024 + 512, delta_g + i * 128, 512, &q_full[s]);
+        mbar_wait(do_empty, (it & 1) ^ 1);
+        mbar_arrive_expect_tx(do_full, L::kTileBytes);
+        for (int hh = 0; hh < kHalves; ++hh)
+          tma_load_4d(&tmDO, do_full, smem + L::kDOOff + hh * L::kHalfBytes, hh * 64, i * 128, h, b);
+      }
+    }
+  } else if (warp == 13) {
+    // ============================== MMA issuer ==============================
+    reg_dealloc<40>();
+    if (lane == 0 && n > 0) {
+      constexpr int kFmt = kBf16 ? 1 : 0;
+      constexpr uint32_t idesc_kk = make_idesc(128, 128, kFmt, 0, 0);  // S^T, dP^T
+      constexpr uint32_t idesc_dv = make_idesc(128, D, kFmt, 0, 1);    // dV (A in TMEM), dK (A K-major)
+      constexpr uint32_t idesc_dq = make_idesc(128, D, kFmt, 1, 1);    // dQ (A and B MN-major)
+      const uint32_t k_addr = smem_u32(smem + L::kKOff), v_addr = smem_u32(smem + L::kVOff);
+      const uint32_t q_addr = smem_u32(smem + L::kQOff), do_addr = smem_u32(smem + L::kDOOff);
+      const uint32_t ds_addr = smem_u32(smem + L::kDSOff);
+      const uint32_t tS = tmem_base + kColS, tDP = tmem_base + kColDP;
+      const uint32_t tDK = tmem_base + kColDK, tDV = tmem_base + kColDV;
+
+      auto issue_kk = [&](uint32_t d_tmem, uint32_t a_addr, uint32_t b_addr) {
+        #pragma unroll
+        for (int k = 0; k < D / 16; ++k) {
+          const uint32_t off = (k / 4) * L::kHalfBytes + (k % 4) * 32;
+          umma_ss(d_tmem, make_smem_desc(a_addr + off, 16, 1024), make_smem_desc(b_addr + off, 16, 1024),
+                  idesc_kk, k > 0);
+        }
+      };
+
+      mbar_wait(kv_full, 0);
+      mbar_wait(&q_full[0], 0);
+      tc_fence_after();
+      issue_kk(tS, k_addr, q_addr);  // S^T(0)
+      umma_commit(s_full);
+      for (int it = 0; it < n; ++it) {
+        const uint32_t q_cur = q_addr + (it & 1) * L::kTileBytes;
+        // dP^T(it) = V dO^T   (overwrites dQ(it-1): the drain must have emptied it)
+        mbar_wait(do_full, it & 1);
+        if (it > 0) mbar_wait(dq_empty, (it - 1) & 1);
+        tc_fence_after();
+        issue_kk(tDP, v_addr, do_addr);
+        umma_commit(dp_full);
+        // dV += P^T dO
+        mbar_wait(p_full, it & 1);
+        tc_fence_after();
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint32_t a_t = tS + (k < 4 ? 8 * k : 64 + 8 * (k - 4));
+          umma_ts(tDV, a_t, make_smem_desc(do_addr + k * 2048, L::kHalfBytes, 1024), idesc_dv,
+                  (it > 0 || k > 0));
+        }
+        umma_commit(do_empty);
+        // S^T(it+1) = K Q^T  (overwrites P^T(it), which dV(it) has consumed by then: in-order pipe)
+        if (it + 1 < n) {
+          mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
+          tc_fence_after();
+          issue_kk(tS, k_addr, q_addr + ((it + 1) & 1) * L::kTileBytes);
+          umma_commit(s_full);
+        }
+        // dQ(it) = dS K ; dK += dS^T Q
+        mbar_wait(ds_full, it & 1);
+        tc_fence_after();
+        #pragma unroll
+        for (int k = 0; k < 8; ++k)
+          umma_ss(tDP, make_smem_desc(ds_addr + k * 2048, L::kHalfBytes, 1024),
+                  make_smem_desc(k_addr + k * 2048, L::kHalfBytes, 1024), idesc_dq, k > 0);
+        umma_commit(dq_full);
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint32_t off = (k / 4) * L::kHalfBytes + (k % 4) * 32;
+          umma_ss(tDK, make_smem_desc(ds_addr + off, 16, 1024),
+                  make_smem_desc(q_cur + k * 2048, L::kHalfBytes, 1024), idesc_dv, (it > 0 || k > 0));
+        }
+        umma_commit(&q_empty[it & 1]);
+      }
+      umma_commit(dkv_full);
+    }
+  } else if (warp >= 8 && warp < 12) {
+    // ============================== dQ drain ==============================
+    reg_dealloc<104>();
+    const int row = (warp & 3) * 32 + lane;  // query row within the tile
+    const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    uint8_t *stage = smem + L::kDQOff;
+    for (int it = 0; it < n; ++it) {
+      const int i = i0 + it;
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      #pragma unroll
+      for (int hh = 0; hh < kHalves; ++hh) {  // 64 fp32 columns at a time
+        uint32_t r[2][32];
+        tmem_ld32(tDQ + hh * 64, r[0]);
+        tmem_ld32(tDQ + hh * 64 + 32, r[1]);
+        tmem_ld_wait();
+        if (hh == kHalves - 1) { tc_fence_before(); mbar_arrive(dq_empty); }
+        // staging may still be read by the previous reduce-add
+        if (threadIdx.x == 256) tma_store_wait_read<0>();
+        named_bar_sync(3, 128);
+        #pragma unroll
+        for (int sl = 0; sl < 2; ++sl)
+          #pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 w = make_uint4(r[sl][c * 4], r[sl][c * 4 + 1], r[sl][c * 4 + 2], r[sl][c * 4 + 3]);
+            *reinterpret_cast<uint4 *>(stage + sl * L::kHalfBytes + row * 128 + ((c ^ (row & 7)) * 16)) = w;
+          }
+        fence_proxy_async_smem();
+        named_bar_sync(3, 128);
+        if (threadIdx.x == 256) {
+          tma_reduce_add_4d(&tmDQ, stage, hh * 64, i * 128, h, b);
+          tma_reduce_add_4d(&tmDQ, stage + L::kHalfBytes, hh * 64 + 32, i * 128, h, b);
+          tma_store_commit();
+        }
+      }
+    }
+    if (threadIdx.x == 256) tma_store_wait<0>();
+  } else if (warp < 8) {
+    // ============================== compute: P^T, dS^T ; epilogue dK, dV ==============================
+    reg_alloc<168>();
+    const int wg = warp >> 2;                      // which 64 query columns of the tile
+    const int row = (warp & 3) * 32 + lane;        // key row within the KV tile (= TMEM lane)
+    const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem_base + kColS + lane_addr + 64 * wg;
+    const uint32_t tDP = tmem_base + kColDP + lane_addr + 64 * wg;
+    uint8_t *ds_row = smem + L::kDSOff + wg * L::kHalfBytes + row * 128;
+    const int key = j * 128 + row;
+
+    for (int it = 0; it < n; ++it) {
+      const int i = i0 + it;
+      const float4 *stat = reinterpret_cast<const float4 *>(smem + L::kStatOff + (it & 1) * 1024) + wg * 16;
+      mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
+      mbar_wait(s_full, it & 1);
+      tc_fence_after();
+      float pr[64];
+      {
+        uint32_t s[2][32];
+        tmem_ld32(tS, s[0]);
+        tmem_ld32(tS + 32, s[1]);
+        tmem_ld_wait();
+        #pragma unroll
+        for (int c4 = 0; c4 < 16; ++c4) {
+          const float4 l4 = stat[c4];
+          const float ls[4] = {l4.x, l4.y, l4.z, l4.w};
+          #pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = c4 * 4 + e;
+            pr[c] = fast_exp2(fmaf(__uint_as_float(s[c >> 5][c & 31]), p.scale_log2, -ls[e]));
+          }
+        }
+      }
+      // causal mask on tiles that cross the diagonal: query column visible iff key <= q + shift
+      if (p.causal && j * 128 + 127 > i * 128 + p.shift) {
+        const int cmin = key - p.shift - i * 128 - 64 * wg;  // columns below cmin are masked
+        #pragma unroll
+        for (int c = 0; c < 64; ++c)
+          if (c < cmin) pr[c] = 0.f;
+      }
+      {
+        uint32_t pk[32];
+        #pragma unroll
+        for (int c = 0; c < 32; ++c) pk[c] = pack2<kBf16>(pr[2 * c], pr[2 * c + 1]);
+        tmem_st32(tS, pk);  // P^T over the first half of this warpgroup's own S^T columns
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(p_full);
+      }
+      // dS^T = P^T o (dP^T - delta)
+      mbar_wait(dp_full, it & 1);
+      tc_fence_after();
+      #pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        uint32_t dp[32];
+        tmem_ld32(tDP + hf * 32, dp);
+        tmem_ld_wait();
+        #pragma unroll
+        for (int c8 = 0; c8 < 4; ++c8) {  // 8 columns -> one 16-byte chunk
+          const float4 d0 = stat[32 + hf * 8 + c8 * 2], d1 = stat[32 + hf * 8 + c8 * 2 + 1];
+          const float dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+          uint32_t w[4];
+          #pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = c8 * 8 + 2 * e;
+            const float a = pr[hf * 32 + c] * (__uint_as_float(dp[c]) - dl[2 * e]);
+            const float bb = pr[hf * 32 + c + 1] * (__uint_as_float(dp[c + 1]) - dl[2 * e + 1]);
+            w[e] = pack2<kBf16>(a, bb);
+          }
+          const int chunk = (hf * 4 + c8) ^ (row & 7);
+          *reinterpret_cast<uint4 *>(ds_row + chunk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(ds_full);
+    }
+
+    // ---------------- epilogue: dK * scale, dV -> smem (SW128) -> TMA store ----------------
+    if (n > 0) {
+      mbar_wait(dkv_full, 0);
+      tc_fence_after();
+    }
+    constexpr int kItems = (D == 128) ? 2 : 1;
+    #pragma unroll
+    for (int item = 0; item < kItems; ++item) {
+      const int which = (D == 128) ? item : wg;   // 0 = dK, 1 = dV
+      const int half = (D == 128) ? wg : 0;       // which 64-column slab
+      const uint32_t tsrc = tmem_base + (which == 0 ? kColDK : kColDV) + lane_addr + 64 * half;
+      const float mul = which == 0 ? p.scale : 1.f;
+      uint8_t *dst_row = smem + L::kQOff + which * L::kTileBytes + half * L::kHalfBytes + row * 128;
+      #pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        uint32_t r[32];
+        if (n > 0) {
+          tmem_ld32(tsrc + hf * 32, r);
+          tmem_ld_wait();
+        } else {
+          #pragma unroll
+          for (int e = 0; e < 32; ++e) r[e] = 0u;
+        }
+        #pragma unroll
+        for (int c8 = 0; c8 < 4; ++c8) {
+          uint32_t w[4];
+          #pragma unroll
+          for (int e = 0; e < 4; ++e)
+            w[e] = pack2<kBf16>(__uint_as_float(r[c8 * 8 + 2 * e]) * mul, __uint_as_float(r[c8 * 8 + 2 * e + 1]) * mul);
+          const int chunk = (hf * 4 + c8) ^ (row & 7);
+          *reinterpret_cast<uint4 *>(dst_row + chunk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(2, 256);
+    if (threadIdx.x == 0) {
+      for (int hh = 0; hh < kHalves; ++hh) {
+        tma_store_4d(&tmDK, smem + L::kQOff + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
+        tma_store_4d(&tmDV, smem + L::kQOff + L::kTileBytes + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
+      }
+      tma_store_commit();
+      tma_store_wait<0>();
+    }
+  } else {
+    reg_dealloc<40>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 14) tmem_dealloc<512>(tmem_base);
+}
+
+// Pre-kernel: delta = rowsum(O o dO) (cpp/flash_attention_qkv_packed.cpp:374-377) and
+// lse2 = lse * log2(e), both padded to a multiple of 128 rows per (batch, head) so that the main
+// kernel can bulk-copy 128-row slices without bounds checks.  One warp per (padded) row.
+template <typename T>
+__global__ void __launch_bounds__(128)
+fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T *dout, int64_t d_sb,
+                   int64_t d_sh, int64_t d_sl, const float *lse, float *delta, float *lse2, int B,
+                   int H, int Lq, int Lq_pad, int D) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t rid = static_cast<int64_t>(blockIdx.x) * 4 + warp;
+  if (rid >= static_cast<int64_t>(B) * H * Lq_pad) return;
+  const int r = static_cast<int>(rid % Lq_pad);
+  const int g = static_cast<int>(rid / Lq_pad);
+  float s = 0.f, l2 = INFINITY;
+  if (r < Lq) {
+    const T *orow = o + (g / H) * o_sb + (g % H) * o_sh + static_cast<int64_t>(r) * o_sl;
+    const T *drow = dout + (g / H) * d_sb + (g % H) * d_sh + static_cast<int64_t>(r) * d_sl;
+    for (int d = lane * 2; d < D; d += 64) {
+      s = fmaf(static_cast<float>(orow[d]), static_cast<float>(drow[d]), s);
+      s = fmaf(static_cast<float>(orow[d + 1]), static_cast<float>(drow[d + 1]), s);
+    }
+    #pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    const float l = lse[static_cast<int64_t>(g) * Lq + r];
+    l2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
+  }
+  if (lane == 0) { delta[rid] = s; lse2[rid] = l2; }
+}
+
+}  // namespace fa

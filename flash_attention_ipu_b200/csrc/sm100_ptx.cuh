@@ -102,6 +102,13 @@ __device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap *m, const vo
       "r"(c3)
       : "memory");
 }
+// 1-D bulk copy global -> shared (16-byte aligned, size multiple of 16), completes on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
