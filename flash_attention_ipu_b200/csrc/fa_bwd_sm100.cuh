@@ -88,7 +88,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t *dkv_full = bars + 13; // MMA -> compute : final dK, dV ready
   uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
   const int g = blockIdx.x / p.num_kv_tiles;
   const int j = blockIdx.x % p.num_kv_tiles;  // ascending: the KV tiles with most Q tiles first
@@ -121,7 +121,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   if (warp == 12) {
     // ============================== TMA producer ==============================
-    reg_dealloc<40>();
+    reg_dealloc<72>();
     if (lane == 0 && n > 0) {
       mbar_arrive_expect_tx(kv_full, 2 * L::kTileBytes);
       for (int hh = 0; hh < kHalves; ++hh) {
@@ -147,78 +147,97 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   } else if (warp == 13) {
     // ============================== MMA issuer ==============================
-    reg_dealloc<40>();
-    if (lane == 0 && n > 0) {
+    // Warp-uniform loop, one elected lane issues; (lo, hi) descriptors with constant offsets.
+    reg_dealloc<72>();
+    if (n > 0) {
       constexpr int kFmt = kBf16 ? 1 : 0;
       constexpr uint32_t idesc_kk = make_idesc(128, 128, kFmt, 0, 0);  // S^T, dP^T
       constexpr uint32_t idesc_dv = make_idesc(128, D, kFmt, 0, 1);    // dV (A in TMEM), dK (A K-major)
       constexpr uint32_t idesc_dq = make_idesc(128, D, kFmt, 1, 1);    // dQ (A and B MN-major)
-      const uint32_t k_addr = smem_u32(smem + L::kKOff), v_addr = smem_u32(smem + L::kVOff);
-      const uint32_t q_addr = smem_u32(smem + L::kQOff), do_addr = smem_u32(smem + L::kDOOff);
-      const uint32_t ds_addr = smem_u32(smem + L::kDSOff);
+      constexpr uint32_t hi = smem_desc_hi(1024);
+      constexpr uint32_t kTile16 = L::kTileBytes >> 4, kHalf16 = L::kHalfBytes >> 4;
+      // K-major views (LBO unused) and MN-major views (LBO = distance between 64-column slabs)
+      const uint32_t k_kmaj = smem_desc_lo(smem_u32(smem + L::kKOff), 16);
+      const uint32_t v_kmaj = smem_desc_lo(smem_u32(smem + L::kVOff), 16);
+      const uint32_t q_kmaj = smem_desc_lo(smem_u32(smem + L::kQOff), 16);
+      const uint32_t do_kmaj = smem_desc_lo(smem_u32(smem + L::kDOOff), 16);
+      const uint32_t ds_kmaj = smem_desc_lo(smem_u32(smem + L::kDSOff), 16);
+      const uint32_t k_mn = smem_desc_lo(smem_u32(smem + L::kKOff), L::kHalfBytes);
+      const uint32_t q_mn = smem_desc_lo(smem_u32(smem + L::kQOff), L::kHalfBytes);
+      const uint32_t do_mn = smem_desc_lo(smem_u32(smem + L::kDOOff), L::kHalfBytes);
+      const uint32_t ds_mn = smem_desc_lo(smem_u32(smem + L::kDSOff), L::kHalfBytes);
       const uint32_t tS = tmem_base + kColS, tDP = tmem_base + kColDP;
       const uint32_t tDK = tmem_base + kColDK, tDV = tmem_base + kColDV;
+      const bool leader = elect_one();
 
-      auto issue_kk = [&](uint32_t d_tmem, uint32_t a_addr, uint32_t b_addr) {
+      auto issue_kk = [&](uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo) {
         #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
-          const uint32_t off = (k / 4) * L::kHalfBytes + (k % 4) * 32;
-          umma_ss(d_tmem, make_smem_desc(a_addr + off, 16, 1024), make_smem_desc(b_addr + off, 16, 1024),
-                  idesc_kk, k > 0);
+          const uint32_t off = ((k / 4) * L::kHalfBytes + (k % 4) * 32) >> 4;
+          umma_ss2(d_tmem, a_lo + off, hi, b_lo + off, hi, idesc_kk, k > 0);
         }
       };
 
       mbar_wait(kv_full, 0);
       mbar_wait(&q_full[0], 0);
       tc_fence_after();
-      issue_kk(tS, k_addr, q_addr);  // S^T(0)
-      umma_commit(s_full);
+      if (leader) {
+        issue_kk(tS, k_kmaj, q_kmaj);  // S^T(0)
+        umma_commit(s_full);
+      }
       for (int it = 0; it < n; ++it) {
-        const uint32_t q_cur = q_addr + (it & 1) * L::kTileBytes;
+        const uint32_t q_stage = (it & 1) * kTile16;
         // dP^T(it) = V dO^T   (overwrites dQ(it-1): the drain must have emptied it)
         mbar_wait(do_full, it & 1);
         if (it > 0) mbar_wait(dq_empty, (it - 1) & 1);
         tc_fence_after();
-        issue_kk(tDP, v_addr, do_addr);
-        umma_commit(dp_full);
+        if (leader) {
+          issue_kk(tDP, v_kmaj, do_kmaj);
+          umma_commit(dp_full);
+        }
         // dV += P^T dO
         mbar_wait(p_full, it & 1);
         tc_fence_after();
-        #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint32_t a_t = tS + (k < 4 ? 8 * k : 64 + 8 * (k - 4));
-          umma_ts(tDV, a_t, make_smem_desc(do_addr + k * 2048, L::kHalfBytes, 1024), idesc_dv,
-                  (it > 0 || k > 0));
+        if (leader) {
+          #pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ts2(tDV, tS + (k < 4 ? 8 * k : 64 + 8 * (k - 4)), do_mn + k * (2048 >> 4), hi, idesc_dv,
+                     (it > 0 || k > 0));
+          umma_commit(do_empty);
         }
-        umma_commit(do_empty);
         // S^T(it+1) = K Q^T  (overwrites P^T(it), which dV(it) has consumed by then: in-order pipe)
         if (it + 1 < n) {
           mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
           tc_fence_after();
-          issue_kk(tS, k_addr, q_addr + ((it + 1) & 1) * L::kTileBytes);
-          umma_commit(s_full);
+          if (leader) {
+            issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16);
+            umma_commit(s_full);
+          }
         }
         // dQ(it) = dS K ; dK += dS^T Q
         mbar_wait(ds_full, it & 1);
         tc_fence_after();
-        #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          umma_ss(tDP, make_smem_desc(ds_addr + k * 2048, L::kHalfBytes, 1024),
-                  make_smem_desc(k_addr + k * 2048, L::kHalfBytes, 1024), idesc_dq, k > 0);
-        umma_commit(dq_full);
-        #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint32_t off = (k / 4) * L::kHalfBytes + (k % 4) * 32;
-          umma_ss(tDK, make_smem_desc(ds_addr + off, 16, 1024),
-                  make_smem_desc(q_cur + k * 2048, L::kHalfBytes, 1024), idesc_dv, (it > 0 || k > 0));
+        if (leader) {
+          #pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ss2(tDP, ds_mn + k * (2048 >> 4), hi, k_mn + k * (2048 >> 4), hi, idesc_dq, k > 0);
+          umma_commit(dq_full);
+          #pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t off = ((k / 4) * L::kHalfBytes + (k % 4) * 32) >> 4;
+            umma_ss2(tDK, ds_kmaj + off, hi, q_mn + q_stage + k * (2048 >> 4), hi, idesc_dv,
+                     (it > 0 || k > 0));
+          }
+          umma_commit(&q_empty[it & 1]);
         }
-        umma_commit(&q_empty[it & 1]);
+        __syncwarp();
       }
-      umma_commit(dkv_full);
+      if (leader) umma_commit(dkv_full);
+      (void)kHalf16;
     }
   } else if (warp >= 8 && warp < 12) {
     // ============================== dQ drain ==============================
-    reg_dealloc<104>();
+    reg_dealloc<96>();
     const int row = (warp & 3) * 32 + lane;  // query row within the tile
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     uint8_t *stage = smem + L::kDQOff;
@@ -377,7 +396,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tma_store_wait<0>();
     }
   } else {
-    reg_dealloc<40>();
+    reg_dealloc<72>();
   }
 
   tc_fence_before();

@@ -89,7 +89,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t *o_full = p_full + 2;                 // [2]  MMA -> softmax : final O_i ready
   uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
 
   // work decode: consecutive CTAs share a (batch, head) so K/V stay in L2; heavy tiles first
@@ -117,12 +117,10 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tmem_S[2] = {tmem_base, tmem_base + 128};
-  const uint32_t tmem_O[2] = {tmem_base + 256, tmem_base + 256 + D};
 
   if (warp == 8) {
     // ============================== TMA producer ==============================
-    reg_dealloc<56>();
+    reg_dealloc<88>();
     if (lane == 0) {
       for (int i = 0; i < 2; ++i) {
         mbar_arrive_expect_tx(&q_full[i], L::kTileBytes);
@@ -146,32 +144,37 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   } else if (warp == 9) {
     // ============================== MMA issuer ==============================
-    reg_dealloc<56>();
-    if (lane == 0) {
+    // The whole warp walks the loop (warp-uniform control flow, waits included); one elected
+    // lane issues the MMAs and their commits.  Descriptors are (lo, hi) words whose per-MMA
+    // offsets are compile-time constants, so an MMA costs a couple of integer instructions.
+    reg_dealloc<88>();
+    {
       constexpr uint32_t idesc_s = make_idesc(kBlockM, kBlockN, kBf16 ? 1 : 0, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc(kBlockM, D, kBf16 ? 1 : 0, 0, 1);
-      const uint32_t q_addr = smem_u32(smem + L::kQOff);
-      const uint32_t k_addr = smem_u32(smem + L::kKOff);
-      const uint32_t v_addr = smem_u32(smem + L::kVOff);
+      constexpr uint32_t hi = smem_desc_hi(1024);
+      const uint32_t q_lo = smem_desc_lo(smem_u32(smem + L::kQOff), 16);
+      const uint32_t k_lo = smem_desc_lo(smem_u32(smem + L::kKOff), 16);
+      const uint32_t v_lo = smem_desc_lo(smem_u32(smem + L::kVOff), L::kHalfBytes);
+      const bool leader = elect_one();
+      const int n0 = n_kv[0], n1 = n_kv[1];
 
       auto issue_s = [&](int i, int j) {  // S_i = Q_i K_j^T   (both operands K-major, SW128)
-        const int ks = j % kKStages;
+        const uint32_t a = q_lo + i * (L::kTileBytes >> 4);
+        const uint32_t bb = k_lo + (j % kKStages) * (L::kTileBytes >> 4);
+        const uint32_t d = tmem_base + i * 128;
         #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
-          const uint32_t off = (k / 4) * L::kHalfBytes + (k % 4) * 32;
-          umma_ss(tmem_S[i], make_smem_desc(q_addr + i * L::kTileBytes + off, 16, 1024),
-                  make_smem_desc(k_addr + ks * L::kTileBytes + off, 16, 1024), idesc_s, k > 0);
+          const uint32_t off = ((k / 4) * L::kHalfBytes + (k % 4) * 32) >> 4;
+          umma_ss2(d, a + off, hi, bb + off, hi, idesc_s, k > 0);
         }
         umma_commit(&s_full[i]);
       };
       auto issue_pv = [&](int i, int j) {  // O_i += P_i V_j   (A = P in TMEM, B = V MN-major)
-        const int vs = j % kVStages;
+        const uint32_t bb = v_lo + (j % kVStages) * (L::kTileBytes >> 4);
+        const uint32_t d = tmem_base + 256 + i * D, a = tmem_base + i * 128;
         #pragma unroll
-        for (int k = 0; k < kBlockN / 16; ++k) {
-          umma_ts(tmem_O[i], tmem_S[i] + k * 8,
-                  make_smem_desc(v_addr + vs * L::kTileBytes + k * 2048, L::kHalfBytes, 1024),
-                  idesc_pv, (j > 0 || k > 0));
-        }
+        for (int k = 0; k < kBlockN / 16; ++k)
+          umma_ts2(d, a + k * 8, bb + k * (2048 >> 4), hi, idesc_pv, (j > 0 || k > 0));
       };
 
       mbar_wait(&q_full[0], 0);
@@ -181,42 +184,47 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           mbar_wait(&k_full[j % kKStages], (j / kKStages) & 1);
           tc_fence_after();
         }
-        if (j < n_kv[0]) {
+        if (j < n0 && leader) {
           issue_s(0, j);
-          if (!(j < n_kv[1])) umma_commit(&k_empty[j % kKStages]);
+          if (!(j < n1)) umma_commit(&k_empty[j % kKStages]);
         }
-        if (j >= 1 && j - 1 < n_kv[1]) {
+        if (j >= 1 && j - 1 < n1) {
           mbar_wait(&v_full[(j - 1) % kVStages], ((j - 1) / kVStages) & 1);
           mbar_wait(&p_full[1], (j - 1) & 1);
           tc_fence_after();
-          issue_pv(1, j - 1);
-          umma_commit(&v_empty[(j - 1) % kVStages]);
-          if (j - 1 == n_kv[1] - 1) umma_commit(&o_full[1]);
+          if (leader) {
+            issue_pv(1, j - 1);
+            umma_commit(&v_empty[(j - 1) % kVStages]);
+            if (j - 1 == n1 - 1) umma_commit(&o_full[1]);
+          }
         }
-        if (j < n_kv[1]) {
+        if (j < n1 && leader) {
           issue_s(1, j);
           umma_commit(&k_empty[j % kKStages]);
         }
-        if (j < n_kv[0]) {
+        if (j < n0) {
           mbar_wait(&v_full[j % kVStages], (j / kVStages) & 1);
           mbar_wait(&p_full[0], j & 1);
           tc_fence_after();
-          issue_pv(0, j);
-          if (!(j < n_kv[1])) umma_commit(&v_empty[j % kVStages]);
-          if (j == n_kv[0] - 1) umma_commit(&o_full[0]);
+          if (leader) {
+            issue_pv(0, j);
+            if (!(j < n1)) umma_commit(&v_empty[j % kVStages]);
+            if (j == n0 - 1) umma_commit(&o_full[0]);
+          }
         }
+        __syncwarp();
       }
     }
   } else if (warp < 8) {
     // ============================== softmax / correction / epilogue ==============================
-    reg_alloc<224>();
+    reg_alloc<208>();
     const int i = warp >> 2;                       // which Q tile
     const int row_in_tile = (warp & 3) * 32 + lane;
     const int row = (t0 + i) * kBlockM + row_in_tile;
     const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t tS = tmem_S[i] + lane_addr;
-    const uint32_t tO = tmem_O[i] + lane_addr;
-    const int n = n_kv[i];
+    const uint32_t tS = tmem_base + i * 128 + lane_addr;
+    const uint32_t tO = tmem_base + 256 + i * D + lane_addr;
+    const int n = i ? n_kv[1] : n_kv[0];
 
     float m_used = -INFINITY;  // reference max (log2 domain) the exponentials are taken against
     float l = 0.f;
@@ -241,11 +249,12 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           for (int e = 0; e < 32; ++e)
             if (c * 32 + e > limit) sr[c][e] = 0xff800000u;  // -inf
       }
-      float mx = -INFINITY;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // 4 independent chains
       #pragma unroll
       for (int c = 0; c < 4; ++c)
         #pragma unroll
-        for (int e = 0; e < 32; ++e) mx = fmaxf(mx, __uint_as_float(sr[c][e]));
+        for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], __uint_as_float(sr[c][e]));
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = mx * p.scale_log2;
 
       // lazy rescale of the running accumulator
@@ -266,7 +275,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (grow) m_used = m_new;
       const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;
 
-      float sum = 0.f;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
       #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t pk[16];
@@ -274,12 +283,12 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int e = 0; e < 32; e += 2) {
           const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c][e]), p.scale_log2, -m_eff));
           const float p1 = fast_exp2(fmaf(__uint_as_float(sr[c][e + 1]), p.scale_log2, -m_eff));
-          sum += p0 + p1;
+          sum4[(e >> 1) & 3] += p0 + p1;
           pk[e >> 1] = pack2<kBf16>(p0, p1);
         }
         tmem_st16(tS + c * 16, pk);
       }
-      l += sum;
+      l += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&p_full[i]);
@@ -327,7 +336,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tma_store_wait<0>();
     }
   } else {
-    reg_dealloc<56>();
+    reg_dealloc<88>();
   }
 
   tc_fence_before();
