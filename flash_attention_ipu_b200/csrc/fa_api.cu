@@ -211,12 +211,10 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   float *lse2 = reinterpret_cast<float *>(ws + ws_stat_bytes(p));
   float *dq_acc = reinterpret_cast<float *>(ws + 2 * ws_stat_bytes(p));
   const int G = p->B * p->H, Lp = lq_pad(p);
-  const size_t acc_bytes = (size_t)G * p->Lq * D * sizeof(float);
-  FA_CUDA_OK(cudaMemsetAsync(dq_acc, 0, acc_bytes, st));
-  fa::fa_bwd_prep_kernel<T><<<blocks_for((int64_t)G * Lp, 4), 128, 0, st>>>(
+  fa::fa_bwd_prep_kernel<T, D><<<blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st>>>(
       reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
       reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
-      delta, lse2, p->B, p->H, p->Lq, Lp, D);
+      delta, lse2, dq_acc, p->B, p->H, p->Lq, Lp);
   if (int rc = launched()) return rc;
 
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
@@ -225,7 +223,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tk, k, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tv, v, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdo, dout, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
-  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 128)) return rc;
+  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32)) return rc;
   if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
@@ -320,7 +318,7 @@ int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
   int fam = family(p);
   if (fam == 1) {
     const size_t es = elem_size(p->dtype);
-    if (!(tma_ok(q, es) && tma_ok(k, es) && tma_ok(v, es) && tma_ok(dout, es) && tma_ok(dq, es) &&
+    if (!(tma_ok(q, es) && tma_ok(k, es) && tma_ok(v, es) && tma_ok(o, es) && tma_ok(dout, es) && tma_ok(dq, es) &&
           tma_ok(dk, es) && tma_ok(dv, es)))
       return fail(FA_B200_ERR_INVALID,
                   "tensor path needs 16-byte aligned pointers and strides (TMA requirement)");

@@ -133,6 +133,14 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int it = 0; it < n; ++it) {
         const int i = i0 + it, s = it & 1;
         mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
+#ifdef FA_EXPERIMENT_HALF_LOADS  // timing experiment only (wrong results): skip every other tile load
+        if ((it & 3) >= 2) {
+          mbar_arrive(&q_full[s]);
+          mbar_wait(do_empty, (it & 1) ^ 1);
+          mbar_arrive(do_full);
+          continue;
+        }
+#endif
         mbar_arrive_expect_tx(&q_full[s], L::kTileBytes + 1024);
         for (int hh = 0; hh < kHalves; ++hh)
           tma_load_4d(&tmQ, &q_full[s], smem + L::kQOff + s * L::kTileBytes + hh * L::kHalfBytes,
@@ -237,41 +245,46 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   } else if (warp >= 8 && warp < 12) {
     // ============================== dQ drain ==============================
-    reg_dealloc<96>();
-    const int row = (warp & 3) * 32 + lane;  // query row within the tile
-    const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    uint8_t *stage = smem + L::kDQOff;
+    // Each warp drains its own 32 query rows independently: TMEM -> registers -> a private
+    // 2 x 4 KB staging ring -> TMA reduce-add (32-row boxes).  No cross-warp barriers, and one
+    // reduce is in flight while the next slab is being staged.
+    reg_dealloc<104>();
+    const int w = warp & 3;
+    const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
+    uint8_t *wstage = smem + L::kDQOff + w * 8192;
     for (int it = 0; it < n; ++it) {
       const int i = i0 + it;
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
       #pragma unroll
-      for (int hh = 0; hh < kHalves; ++hh) {  // 64 fp32 columns at a time
+      for (int hh = 0; hh < kHalves; ++hh) {  // 64 fp32 columns (two 32-column slabs) at a time
         uint32_t r[2][32];
         tmem_ld32(tDQ + hh * 64, r[0]);
         tmem_ld32(tDQ + hh * 64 + 32, r[1]);
         tmem_ld_wait();
         if (hh == kHalves - 1) { tc_fence_before(); mbar_arrive(dq_empty); }
-        // staging may still be read by the previous reduce-add
-        if (threadIdx.x == 256) tma_store_wait_read<0>();
-        named_bar_sync(3, 128);
         #pragma unroll
-        for (int sl = 0; sl < 2; ++sl)
+        for (int sl = 0; sl < 2; ++sl) {
+          uint8_t *buf = wstage + sl * 4096;
+          if (lane == 0) tma_store_wait_read<1>();  // the reduce that last used this buffer has read it
+          __syncwarp();
           #pragma unroll
           for (int c = 0; c < 8; ++c) {
-            uint4 w = make_uint4(r[sl][c * 4], r[sl][c * 4 + 1], r[sl][c * 4 + 2], r[sl][c * 4 + 3]);
-            *reinterpret_cast<uint4 *>(stage + sl * L::kHalfBytes + row * 128 + ((c ^ (row & 7)) * 16)) = w;
+            uint4 v4 = make_uint4(r[sl][c * 4], r[sl][c * 4 + 1], r[sl][c * 4 + 2], r[sl][c * 4 + 3]);
+            *reinterpret_cast<uint4 *>(buf + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
           }
-        fence_proxy_async_smem();
-        named_bar_sync(3, 128);
-        if (threadIdx.x == 256) {
-          tma_reduce_add_4d(&tmDQ, stage, hh * 64, i * 128, h, b);
-          tma_reduce_add_4d(&tmDQ, stage + L::kHalfBytes, hh * 64 + 32, i * 128, h, b);
-          tma_store_commit();
+          fence_proxy_async_smem();
+          __syncwarp();
+#ifndef FA_EXPERIMENT_NO_REDUCE
+          if (lane == 0) {
+            tma_reduce_add_4d(&tmDQ, buf, hh * 64 + sl * 32, i * 128 + w * 32, h, b);
+            tma_store_commit();
+          }
+#endif
         }
       }
     }
-    if (threadIdx.x == 256) tma_store_wait<0>();
+    if (lane == 0) tma_store_wait<0>();
   } else if (warp < 8) {
     // ============================== compute: P^T, dS^T ; epilogue dK, dV ==============================
     reg_alloc<168>();
@@ -406,31 +419,38 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
 // Pre-kernel: delta = rowsum(O o dO) (cpp/flash_attention_qkv_packed.cpp:374-377) and
 // lse2 = lse * log2(e), both padded to a multiple of 128 rows per (batch, head) so that the main
-// kernel can bulk-copy 128-row slices without bounds checks.  One warp per (padded) row.
-template <typename T>
-__global__ void __launch_bounds__(128)
+// kernel can bulk-copy 128-row slices without bounds checks; also zeroes the fp32 dQ accumulator
+// row (saves a separate memset pass).  D/8 threads per row, 16-byte loads.
+template <typename T, int D>
+__global__ void __launch_bounds__(256)
 fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T *dout, int64_t d_sb,
-                   int64_t d_sh, int64_t d_sl, const float *lse, float *delta, float *lse2, int B,
-                   int H, int Lq, int Lq_pad, int D) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t rid = static_cast<int64_t>(blockIdx.x) * 4 + warp;
-  if (rid >= static_cast<int64_t>(B) * H * Lq_pad) return;
-  const int r = static_cast<int>(rid % Lq_pad);
-  const int g = static_cast<int>(rid / Lq_pad);
+                   int64_t d_sh, int64_t d_sl, const float *lse, float *delta, float *lse2,
+                   float *dq_acc, int B, int H, int Lq, int Lq_pad) {
+  constexpr int kTpr = D / 8;  // threads per row
+  const int sub = threadIdx.x % kTpr;
+  const int64_t rid = static_cast<int64_t>(blockIdx.x) * (256 / kTpr) + threadIdx.x / kTpr;
+  const bool in_range = rid < static_cast<int64_t>(B) * H * Lq_pad;
+  const int r = in_range ? static_cast<int>(rid % Lq_pad) : Lq;
+  const int g = in_range ? static_cast<int>(rid / Lq_pad) : 0;
   float s = 0.f, l2 = INFINITY;
   if (r < Lq) {
-    const T *orow = o + (g / H) * o_sb + (g % H) * o_sh + static_cast<int64_t>(r) * o_sl;
-    const T *drow = dout + (g / H) * d_sb + (g % H) * d_sh + static_cast<int64_t>(r) * d_sl;
-    for (int d = lane * 2; d < D; d += 64) {
-      s = fmaf(static_cast<float>(orow[d]), static_cast<float>(drow[d]), s);
-      s = fmaf(static_cast<float>(orow[d + 1]), static_cast<float>(drow[d + 1]), s);
-    }
+    const T *orow = o + (g / H) * o_sb + (g % H) * o_sh + static_cast<int64_t>(r) * o_sl + sub * 8;
+    const T *drow = dout + (g / H) * d_sb + (g % H) * d_sh + static_cast<int64_t>(r) * d_sl + sub * 8;
+    const uint4 ov = *reinterpret_cast<const uint4 *>(orow);
+    const uint4 dv = *reinterpret_cast<const uint4 *>(drow);
+    const T *oe = reinterpret_cast<const T *>(&ov);
+    const T *de = reinterpret_cast<const T *>(&dv);
     #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    for (int e = 0; e < 8; ++e) s = fmaf(static_cast<float>(oe[e]), static_cast<float>(de[e]), s);
+    float4 *acc = reinterpret_cast<float4 *>(dq_acc + (static_cast<int64_t>(g) * Lq + r) * D + sub * 8);
+    acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
     const float l = lse[static_cast<int64_t>(g) * Lq + r];
     l2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
   }
-  if (lane == 0) { delta[rid] = s; lse2[rid] = l2; }
+  #pragma unroll
+  for (int off = kTpr / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+  if (in_range && sub == 0) { delta[rid] = s; lse2[rid] = l2; }
 }
 
 }  // namespace fa
