@@ -55,20 +55,22 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.stop_flag = index, [], threading.Event()
+        self.index, self.samples, self.proc = index, [], None
 
     def run(self):
-        while not self.stop_flag.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                self.samples.append([x.strip() for x in out.strip().split(",")])
-            except Exception:
-                pass
-            self.stop_flag.wait(0.1)
+        # one long-lived nvidia-smi in loop mode (a fresh process per sample is too slow for
+        # timed regions of a few hundred ms)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "20"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                self.samples.append([x.strip() for x in line.strip().split(",")])
+        except Exception:
+            pass
 
     def summary(self):
-        self.stop_flag.set()
+        if self.proc is not None:
+            self.proc.terminate()
         self.join(timeout=6)
         mhz = sorted(int(s[0]) for s in self.samples if len(s) >= 7 and s[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -171,6 +173,7 @@ def run_ours(args):
     # ---- timed region: device-resident inputs, CUDA events on the launch stream
     sampler = ClockSampler(local_rank)
     sampler.start()
+    time.sleep(0.3)
     launches0 = native.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     barrier()
@@ -271,7 +274,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
