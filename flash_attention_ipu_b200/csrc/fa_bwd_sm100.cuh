@@ -29,10 +29,14 @@
 namespace fa {
 
 constexpr int kBwdThreads = 512;
+#ifndef FA_BWD_POLY_EVERY
+#define FA_BWD_POLY_EVERY 4
+#endif
+constexpr int kBwdPolyEvery = FA_BWD_POLY_EVERY;  // every n-th pair of exponentials runs on the FMA pipe (0: none)
 
 struct BwdParams {
-  const float *lse2;   // [G][Lq_pad]  lse * log2(e); +inf for padding / rows without keys
-  const float *delta;  // [G][Lq_pad]  rowsum(O o dO); 0 for padding
+  const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
+  const float *delta;  // [G][Lq_pad]  -rowsum(O o dO); 0 for padding
   int Lq, Lk, H, Lq_pad;
   int causal, shift;
   float scale, scale_log2;
@@ -300,6 +304,14 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const int i = i0 + it;
       const float4 *stat = reinterpret_cast<const float4 *>(smem + L::kStatOff + (it & 1) * 1024) + wg * 16;
       mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
+      // -lse2 of this warpgroup's 64 query columns: loaded (broadcast LDS.128) BEFORE the S^T wait so
+      // that the shared-memory latency hides behind it
+      float nl[64];
+      #pragma unroll
+      for (int c4 = 0; c4 < 16; ++c4) {
+        const float4 l4 = stat[c4];
+        nl[4 * c4] = l4.x; nl[4 * c4 + 1] = l4.y; nl[4 * c4 + 2] = l4.z; nl[4 * c4 + 3] = l4.w;
+      }
       mbar_wait(s_full, it & 1);
       tc_fence_after();
       float pr[64];
@@ -308,14 +320,18 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tmem_ld32(tS, s[0]);
         tmem_ld32(tS + 32, s[1]);
         tmem_ld_wait();
+        const uint64_t c2 = f2_pack(p.scale_log2, p.scale_log2);
         #pragma unroll
-        for (int c4 = 0; c4 < 16; ++c4) {
-          const float4 l4 = stat[c4];
-          const float ls[4] = {l4.x, l4.y, l4.z, l4.w};
-          #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int c = c4 * 4 + e;
-            pr[c] = fast_exp2(fmaf(__uint_as_float(s[c >> 5][c & 31]), p.scale_log2, -ls[e]));
+        for (int c = 0; c < 64; c += 2) {
+          float x0, x1;
+          f2_unpack(f2_fma(f2_pack(s[c >> 5][c & 31], s[c >> 5][(c & 31) + 1]), c2, f2_pack(nl[c], nl[c + 1])),
+                    x0, x1);
+          constexpr int kEvery = kBwdPolyEvery > 0 ? kBwdPolyEvery : 1;
+          if (kBwdPolyEvery > 0 && (c >> 1) % kEvery == kEvery - 1) {  // this pair on the FMA pipe
+            poly_exp2_pair(x0, x1, pr[c], pr[c + 1]);
+          } else {
+            pr[c] = fast_exp2(x0);
+            pr[c + 1] = fast_exp2(x1);
           }
         }
       }
@@ -335,7 +351,14 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tc_fence_before();
         mbar_arrive(p_full);
       }
-      // dS^T = P^T o (dP^T - delta)
+      // dS^T = P^T o (dP^T - delta); -delta of each 32-column half is fetched ahead of the
+      // barrier / TMEM load it is used after
+      float nd[32];
+      #pragma unroll
+      for (int c4 = 0; c4 < 8; ++c4) {
+        const float4 d4 = stat[32 + c4];
+        nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
+      }
       mbar_wait(dp_full, it & 1);
       tc_fence_after();
       #pragma unroll
@@ -343,20 +366,26 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         uint32_t dp[32];
         tmem_ld32(tDP + hf * 32, dp);
         tmem_ld_wait();
+        uint32_t w[16];
+        #pragma unroll
+        for (int c = 0; c < 32; c += 2) {
+          float a0, a1;
+          f2_unpack(f2_mul(f2_pack(pr[hf * 32 + c], pr[hf * 32 + c + 1]),
+                           f2_add(f2_pack(dp[c], dp[c + 1]), f2_pack(nd[c], nd[c + 1]))), a0, a1);
+          w[c >> 1] = pack2<kBf16>(a0, a1);
+        }
+        if (hf == 0) {
+          #pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            const float4 d4 = stat[40 + c4];
+            nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
+          }
+        }
         #pragma unroll
         for (int c8 = 0; c8 < 4; ++c8) {  // 8 columns -> one 16-byte chunk
-          const float4 d0 = stat[32 + hf * 8 + c8 * 2], d1 = stat[32 + hf * 8 + c8 * 2 + 1];
-          const float dl[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-          uint32_t w[4];
-          #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int c = c8 * 8 + 2 * e;
-            const float a = pr[hf * 32 + c] * (__uint_as_float(dp[c]) - dl[2 * e]);
-            const float bb = pr[hf * 32 + c + 1] * (__uint_as_float(dp[c + 1]) - dl[2 * e + 1]);
-            w[e] = pack2<kBf16>(a, bb);
-          }
           const int chunk = (hf * 4 + c8) ^ (row & 7);
-          *reinterpret_cast<uint4 *>(ds_row + chunk * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+          *reinterpret_cast<uint4 *>(ds_row + chunk * 16) =
+              make_uint4(w[4 * c8], w[4 * c8 + 1], w[4 * c8 + 2], w[4 * c8 + 3]);
         }
       }
       fence_proxy_async_smem();
@@ -417,8 +446,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 14) tmem_dealloc<512>(tmem_base);
 }
 
-// Pre-kernel: delta = rowsum(O o dO) (cpp/flash_attention_qkv_packed.cpp:374-377) and
-// lse2 = lse * log2(e), both padded to a multiple of 128 rows per (batch, head) so that the main
+// Pre-kernel: delta = -rowsum(O o dO) (cpp/flash_attention_qkv_packed.cpp:374-377) and
+// lse2 = -lse * log2(e) (both stored NEGATED so the main kernel folds them in with packed
+// fma/add and no negate modifier; -inf for padded rows and rows without keys => P = 0), both padded to a multiple of 128 rows per (batch, head) so that the main
 // kernel can bulk-copy 128-row slices without bounds checks; also zeroes the fp32 dQ accumulator
 // row (saves a separate memset pass).  D/8 threads per row, 16-byte loads.
 template <typename T, int D>
@@ -432,7 +462,7 @@ fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T
   const bool in_range = rid < static_cast<int64_t>(B) * H * Lq_pad;
   const int r = in_range ? static_cast<int>(rid % Lq_pad) : Lq;
   const int g = in_range ? static_cast<int>(rid / Lq_pad) : 0;
-  float s = 0.f, l2 = INFINITY;
+  float s = 0.f, l2 = -INFINITY;
   if (r < Lq) {
     const T *orow = o + (g / H) * o_sb + (g % H) * o_sh + static_cast<int64_t>(r) * o_sl + sub * 8;
     const T *drow = dout + (g / H) * d_sb + (g % H) * d_sh + static_cast<int64_t>(r) * d_sl + sub * 8;
@@ -446,11 +476,11 @@ fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T
     acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
     acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
     const float l = lse[static_cast<int64_t>(g) * Lq + r];
-    l2 = (l == -INFINITY) ? INFINITY : l * kLog2e;
+    l2 = (l == -INFINITY) ? -INFINITY : -l * kLog2e;
   }
   #pragma unroll
   for (int off = kTpr / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
-  if (in_range && sub == 0) { delta[rid] = s; lse2[rid] = l2; }
+  if (in_range && sub == 0) { delta[rid] = -s; lse2[rid] = l2; }
 }
 
 }  // namespace fa

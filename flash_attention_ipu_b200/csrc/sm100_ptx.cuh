@@ -298,6 +298,67 @@ __device__ __forceinline__ float fast_exp2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// ------------------------------------------------------------------ packed fp32 pairs (FFMA2/FADD2/FMUL2)
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_pack(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_sub(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_add_rm(uint64_t a, uint64_t b) {  // round toward -inf
+  uint64_t d;
+  asm("add.rm.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// 2^x for a pair on the FMA pipe instead of MUFU (the SFU is co-critical with the tensor pipe in
+// attention): Cody-Waite split x = floor(x) + f, degree-3 minimax polynomial for 2^f on [0,1)
+// (max relative error 8.6e-5, far below the 16-bit rounding P receives afterwards), exponent
+// patched in by integer add.  Inputs are clamped at -126 (result 2^-126 ~ 0 for masked scores).
+__device__ __forceinline__ void poly_exp2_pair(float x0, float x1, float &y0, float &y1) {
+  constexpr float kMagic = 12582912.f;  // 1.5 * 2^23: low mantissa bits of (x + magic) = floor(x)
+  x0 = fmaxf(x0, -126.f);
+  x1 = fmaxf(x1, -126.f);
+  const uint64_t x = f2_pack(x0, x1);
+  const uint64_t xr = f2_add_rm(x, f2_pack(kMagic, kMagic));
+  const uint64_t fl = f2_sub(xr, f2_pack(kMagic, kMagic));
+  const uint64_t fr = f2_sub(x, fl);
+  uint64_t p = f2_fma(f2_pack(0.07706726823f, 0.07706726823f), fr, f2_pack(0.22764474478f, 0.22764474478f));
+  p = f2_fma(p, fr, f2_pack(0.69511684188f, 0.69511684188f));
+  p = f2_fma(p, fr, f2_pack(1.f, 1.f));
+  float p0, p1, r0, r1;
+  f2_unpack(p, p0, p1);
+  f2_unpack(xr, r0, r1);
+  y0 = __int_as_float(__float_as_int(p0) + (__float_as_int(r0) << 23));
+  y1 = __int_as_float(__float_as_int(p1) + (__float_as_int(r1) << 23));
+}
+
 // pack two fp32 into one 32-bit word of two 16-bit floats (lo = a, hi = b)
 template <bool kBf16>
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
