@@ -271,6 +271,68 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_ring(args):
+    """--workload ring: BASELINE.json configs[4] -- causal attention over ONE long sequence
+    (T=131072, 32 heads, d=128, bf16) sharded zig-zag over the N GPUs, K/V exchanged by NCCL P2P
+    around a ring with an fp32 LSE merge per hop (flash_attention_ipu_b200/ring.py).  Total work is
+    fixed ("scaling": "strong").  Not the default bench line; the driver's contract line is run_ours."""
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev, init_method=None if world > 1 else "tcp://127.0.0.1:29533",
+                            rank=rank, world_size=world)
+    from flash_attention_ipu_b200 import ring
+    from flash_attention_ipu_b200._impl import native
+    B, H, T, D = 1, 32, args.ring_seq, 128
+    L2 = T // world
+    torch.manual_seed(SEED + rank)
+    q, k, v = (torch.randn(B, H, L2, D, device=dev).bfloat16().requires_grad_(True) for _ in range(3))
+    dout = torch.randn(B, H, L2, D, device=dev).bfloat16()
+
+    def step():
+        q.grad = k.grad = v.grad = None
+        ring.ring_attention(q, k, v).backward(dout)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.3)
+    launches0 = native.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    barrier()
+    ev[0].record()
+    for _ in range(args.steps):
+        step()
+    ev[1].record()
+    barrier()
+    t = torch.tensor([ev[0].elapsed_time(ev[1])], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item() / args.steps
+    flops = attention_flops(B * H, T, D)
+    line = {
+        "metric": METRIC, "value": flops / (ms_step * 1e-3) / 1e12, "unit": "TFLOP/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"long_ctx_T{T}_H{H}_d{D}_bf16_causal_ring", "rows_per_gpu": L2,
+                   "parallelism": f"sequence sharded zig-zag over {world} GPU(s); ring KV exchange by NCCL P2P "
+                                  f"({2 * B * H * L2 * D * 2} B per hop per rank) + fp32 LSE merge",
+                   "l2": "per-rank K/V shards larger than L2 for world<=8"},
+        "clocks": sampler.summary(), "gpu_launches": native.launch_count() - launches0,
+    }
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -278,10 +340,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="llama", choices=["llama", "ring"],
+                    help="llama: configs[2], the contract line (default); ring: configs[4] long-context ring")
+    ap.add_argument("--ring-seq", type=int, default=131072)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "ring":
+        run_ring(args)
     else:
         run_ours(args)
 

@@ -15,7 +15,7 @@ FA_B200_F16, FA_B200_BF16, FA_B200_F32 = 0, 1, 2
 _DTYPES = {torch.float16: FA_B200_F16, torch.bfloat16: FA_B200_BF16, torch.float32: FA_B200_F32}
 
 EXPORTED_SYMBOLS = (
-    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_merge",
+    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_merge", "fa_b200_merge_acc",
     "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_last_error", "fa_b200_version",
 )
 
@@ -41,6 +41,9 @@ _lib.fa_b200_bwd_workspace_bytes.argtypes = [_PP]
 _lib.fa_b200_bwd_workspace_bytes.restype = c_size_t
 _lib.fa_b200_merge.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]
 _lib.fa_b200_merge.restype = c_int
+_lib.fa_b200_merge_acc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
+                                   c_int32, c_int32, c_void_p]
+_lib.fa_b200_merge_acc.restype = c_int
 _lib.fa_b200_kernel_family.argtypes = [_PP]
 _lib.fa_b200_kernel_family.restype = c_int
 _lib.fa_b200_launch_count.argtypes = []
@@ -131,3 +134,20 @@ def merge(o_a, lse_a, o_b, lse_b) -> None:
         rc = _lib.fa_b200_merge(o_a.data_ptr(), lse_a.data_ptr(), o_b.data_ptr(), lse_b.data_ptr(),
                                 rows, D, _DTYPES[o_a.dtype], _stream(o_a))
     _check(rc, "fa_b200_merge")
+
+
+def merge_acc(o_acc, lse_acc, o_b, lse_b, row0: int = 0) -> None:
+    """Fold a hop's partial result into the fp32 ring accumulators, in place.
+
+    o_acc (G, La, D) fp32, lse_acc (G, La) fp32, o_b (G, Lb, D) kernel dtype, lse_b (G, Lb) fp32,
+    all contiguous; partial row r of a group lands on accumulator row ``row0 + r``."""
+    _require_cuda(o_acc, lse_acc, o_b, lse_b)
+    assert o_acc.dtype == torch.float32 and lse_acc.dtype == torch.float32 and lse_b.dtype == torch.float32
+    assert o_acc.is_contiguous() and lse_acc.is_contiguous() and o_b.is_contiguous() and lse_b.is_contiguous()
+    G, La, D = o_acc.shape
+    Gb, Lb, Db = o_b.shape
+    assert G == Gb and D == Db and row0 + Lb <= La
+    with torch.cuda.device(o_acc.device):
+        rc = _lib.fa_b200_merge_acc(o_acc.data_ptr(), lse_acc.data_ptr(), o_b.data_ptr(), lse_b.data_ptr(),
+                                    G, Lb, La, row0, D, _DTYPES[o_b.dtype], _stream(o_acc))
+    _check(rc, "fa_b200_merge_acc")

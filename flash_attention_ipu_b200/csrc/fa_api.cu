@@ -360,4 +360,31 @@ int fa_b200_merge(void *o_a, float *lse_a, const void *o_b, const float *lse_b, 
   return launched();
 }
 
+int fa_b200_merge_acc(float *o_acc, float *lse_acc, const void *o_b, const float *lse_b,
+                      int64_t n_outer, int64_t n_inner, int64_t acc_outer_stride, int64_t acc_row0,
+                      int32_t D, int32_t dtype_b, void *stream) {
+  if (!o_acc || !lse_acc || !o_b || !lse_b || n_outer <= 0 || n_inner <= 0 || D <= 0 ||
+      acc_row0 < 0 || acc_row0 + n_inner > acc_outer_stride)
+    return fail(FA_B200_ERR_INVALID, "bad merge_acc arguments");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const unsigned grid = blocks_for(n_outer * n_inner, 4);
+  switch (dtype_b) {
+    case FA_B200_F32:
+      fa::fa_merge_acc_kernel<float><<<grid, 128, 0, st>>>(o_acc, lse_acc, (const float *)o_b, lse_b,
+                                                           n_outer, n_inner, acc_outer_stride, acc_row0, D);
+      break;
+    case FA_B200_F16:
+      fa::fa_merge_acc_kernel<__half><<<grid, 128, 0, st>>>(o_acc, lse_acc, (const __half *)o_b, lse_b,
+                                                            n_outer, n_inner, acc_outer_stride, acc_row0, D);
+      break;
+    case FA_B200_BF16:
+      fa::fa_merge_acc_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(
+          o_acc, lse_acc, (const __nv_bfloat16 *)o_b, lse_b, n_outer, n_inner, acc_outer_stride, acc_row0, D);
+      break;
+    default:
+      return fail(FA_B200_ERR_UNSUPPORTED, "unknown dtype %d", dtype_b);
+  }
+  return launched();
+}
+
 }  // extern "C"

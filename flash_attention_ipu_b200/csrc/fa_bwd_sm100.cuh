@@ -272,6 +272,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           uint8_t *buf = wstage + sl * 4096;
           if (lane == 0) tma_store_wait_read<1>();  // the reduce that last used this buffer has read it
           __syncwarp();
+#ifdef FA_EXPERIMENT_NO_DRAIN_STS  // timing experiment only (wrong results)
+          asm volatile("" ::"r"(r[sl][0]), "r"(r[sl][31]));
+          continue;
+#endif
           #pragma unroll
           for (int c = 0; c < 8; ++c) {
             uint4 v4 = make_uint4(r[sl][c * 4], r[sl][c * 4 + 1], r[sl][c * 4 + 2], r[sl][c * 4 + 3]);

@@ -32,6 +32,11 @@ constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+#ifndef FA_FWD_POLY_EVERY
+#define FA_FWD_POLY_EVERY 4
+#endif
+constexpr int kFwdPolyEvery = FA_FWD_POLY_EVERY;  // every n-th pair of exponentials on the FMA pipe (0: none)
+template <bool B> struct BoolC { static constexpr bool value = B; };
 constexpr float kRescaleThreshold = 8.0f;  // lazy O rescale: only when the max grows by > 2^8
 
 struct FwdParams {
@@ -249,11 +254,12 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           for (int e = 0; e < 32; ++e)
             if (c * 32 + e > limit) sr[c][e] = 0xff800000u;  // -inf
       }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // 4 independent chains
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // 4 independent 3-input chains
       #pragma unroll
       for (int c = 0; c < 4; ++c)
         #pragma unroll
-        for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], __uint_as_float(sr[c][e]));
+        for (int e = 0; e < 32; e += 2)
+          mx4[(e >> 1) & 3] = fmax3(mx4[(e >> 1) & 3], __uint_as_float(sr[c][e]), __uint_as_float(sr[c][e + 1]));
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = mx * p.scale_log2;
 
@@ -275,20 +281,39 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (grow) m_used = m_new;
       const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;
 
-      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
-      #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t pk[16];
+      // P = exp2(S * scale_log2 - m): packed FFMA2 for the argument; every kFwdPolyEvery-th pair of
+      // exponentials runs as a polynomial on the FMA pipe instead of MUFU (never on masked tiles:
+      // the polynomial clamps at 2^-126 instead of returning an exact 0 for -inf)
+      const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2), nm2 = f2_pack(-m_eff, -m_eff);
+      uint64_t sum2[4] = {0ull, 0ull, 0ull, 0ull};
+      auto exp_tile = [&](auto use_poly) {
         #pragma unroll
-        for (int e = 0; e < 32; e += 2) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c][e]), p.scale_log2, -m_eff));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(sr[c][e + 1]), p.scale_log2, -m_eff));
-          sum4[(e >> 1) & 3] += p0 + p1;
-          pk[e >> 1] = pack2<kBf16>(p0, p1);
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pk[16];
+          #pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            float x0, x1, p0, p1;
+            f2_unpack(f2_fma(f2_pack(sr[c][e], sr[c][e + 1]), sc2, nm2), x0, x1);
+            constexpr int kEvery = kFwdPolyEvery > 0 ? kFwdPolyEvery : 1;
+            if (decltype(use_poly)::value && kFwdPolyEvery > 0 && (e >> 1) % kEvery == kEvery - 1) {
+              poly_exp2_pair(x0, x1, p0, p1);
+            } else {
+              p0 = fast_exp2(x0);
+              p1 = fast_exp2(x1);
+            }
+            sum2[(e >> 1) & 3] = f2_add(sum2[(e >> 1) & 3], f2_pack(p0, p1));
+            pk[e >> 1] = pack2<kBf16>(p0, p1);
+          }
+          tmem_st16(tS + c * 16, pk);
         }
-        tmem_st16(tS + c * 16, pk);
+      };
+      if (tile_masked) exp_tile(BoolC<false>{}); else exp_tile(BoolC<true>{});
+      {
+        float a0, a1, b0, b1;
+        f2_unpack(f2_add(f2_add(sum2[0], sum2[1]), f2_add(sum2[2], sum2[3])), a0, a1);
+        (void)b0; (void)b1;
+        l += a0 + a1;
       }
-      l += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&p_full[i]);

@@ -271,6 +271,34 @@ fa_merge_kernel(T *o_a, float *lse_a, const T *o_b, const float *lse_b, int64_t 
   if (lane == 0) lse_a[rid] = lse;
 }
 
+// Ring-attention accumulator form: the running (o_acc, lse_acc) stay in fp32 for the whole ring
+// (no per-hop rounding) and a hop's partial (o_b in the kernel dtype, lse_b) is folded in.  The
+// partial may cover a sub-range of each group's rows: partial row (g, r) lands on accumulator row
+// g * acc_outer_stride + acc_row0 + r.  One warp per row, D/32 elements per lane.
+template <typename T>
+__global__ void __launch_bounds__(128)
+fa_merge_acc_kernel(float *o_acc, float *lse_acc, const T *o_b, const float *lse_b, int64_t n_outer,
+                    int64_t n_inner, int64_t acc_outer_stride, int64_t acc_row0, int D) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t rid = static_cast<int64_t>(blockIdx.x) * 4 + warp;
+  if (rid >= n_outer * n_inner) return;
+  const int64_t arow = (rid / n_inner) * acc_outer_stride + acc_row0 + rid % n_inner;
+  const float la = lse_acc[arow], lb = lse_b[rid];
+  const float mx = fmaxf(la, lb);
+  float wa = 0.f, wb = 0.f, lse = -INFINITY;
+  if (mx > -INFINITY) {
+    const float ea = __expf(la - mx), eb = __expf(lb - mx);
+    const float inv = 1.f / (ea + eb);
+    wa = ea * inv; wb = eb * inv;
+    lse = mx + __logf(ea + eb);
+  }
+  float *ra = o_acc + arow * D;
+  const T *rb = o_b + rid * D;
+  for (int d = lane; d < D; d += 32) ra[d] = (wa == 0.f ? 0.f : ra[d] * wa) + to_f32(rb[d]) * wb;
+  __syncwarp();
+  if (lane == 0) lse_acc[arow] = lse;
+}
+
 // ------------------------------------------------------------------ fp32 accumulator -> output dtype
 // dQ is accumulated in fp32 by TMA reduce-add in the tensor-path backward; this casts (and scales).
 template <typename T>

@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+$CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
+ncu --set full --clock-control none --import-source on -k regex:fa_${K:-bwd}_sm100 -s 3 -c 1 -o gpurun_out/prof_${K:-bwd} -f $CMD > gpurun_out/ncu_${K:-bwd}.log 2>&1
+tail -2 gpurun_out/plain.log | cut -c1-300

@@ -86,6 +86,14 @@ size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p);
 int fa_b200_merge(void *o_a, float *lse_a, const void *o_b, const float *lse_b, int64_t rows,
                   int32_t D, int32_t dtype, void *stream);
 
+/* Ring accumulator form of the merge: (o_acc, lse_acc) are fp32 and persist across all hops of
+ * a ring (no per-hop rounding); the hop's partial (o_b in dtype_b, lse_b) has n_outer groups of
+ * n_inner rows and partial row (g, r) is folded into accumulator row
+ * g*acc_outer_stride + acc_row0 + r.  lse_acc = -inf marks an empty accumulator row. */
+int fa_b200_merge_acc(float *o_acc, float *lse_acc, const void *o_b, const float *lse_b,
+                      int64_t n_outer, int64_t n_inner, int64_t acc_outer_stride, int64_t acc_row0,
+                      int32_t D, int32_t dtype_b, void *stream);
+
 /* Which kernel family a problem dispatches to: 1 = tcgen05/TMA sm_100a kernels,
  * 0 = generic SIMT kernels (fp32 inputs / head dims the tensor path does not cover),
  * negative = unsupported. */

@@ -232,3 +232,55 @@ def test_errors_are_loud():
     q = torch.zeros(1, 1, 128, 512, device="cuda", dtype=torch.bfloat16)
     with pytest.raises(RuntimeError, match="fa_b200_fwd failed"):
         native.fwd(native.make_problem(q, q, True, 1.0), q, q, q, q, torch.zeros(1, 1, 128, device="cuda"))
+
+
+def test_merge_acc_kernel():
+    """fa_b200_merge_acc (fp32 ring accumulators, sub-range of rows) vs the oracle's merge."""
+    native = _native_loaded()
+    torch.manual_seed(SEED)
+    G, La, Lb, D, row0 = 3, 96, 40, 128, 56
+    o_acc, lse_acc = torch.randn(G, La, D), torch.randn(G, La)
+    lse_acc[0, 60] = float("-inf")  # empty accumulator row: takes the partial as is
+    o_b, lse_b = torch.randn(G, Lb, D).bfloat16(), torch.randn(G, Lb)
+    lse_b[1, 3] = float("-inf")     # empty partial row: accumulator unchanged
+    o_ref, lse_ref = o_acc.clone(), lse_acc.clone()
+    o_m, lse_m = ao.merge_partials(o_acc[:, row0:row0 + Lb], lse_acc[:, row0:row0 + Lb], o_b.float(), lse_b)
+    o_ref[:, row0:row0 + Lb], lse_ref[:, row0:row0 + Lb] = o_m, lse_m
+    o_d, lse_d = o_acc.cuda(), lse_acc.cuda()
+    native.merge_acc(o_d, lse_d, o_b.cuda(), lse_b.cuda(), row0)
+    torch.cuda.synchronize()
+    assert torch.allclose(lse_d.cpu(), lse_ref, atol=1e-5)
+    ok = ~torch.isnan(o_ref)
+    assert torch.allclose(o_d.cpu()[ok], o_ref[ok], atol=1e-5)
+    assert not torch.isnan(o_d).any()
+
+
+@pytest.mark.parametrize("world,T,D", [(2, 1024, 128), (4, 2048, 64), (8, 4096, 128)])
+def test_emulated_ring_vs_single_gpu_and_oracle(world, T, D):
+    """Config-5 schedule (zig-zag shards, one block per hop, fp32 LSE merge, travelling dK/dV) with
+    every rank stepped on one GPU: must agree with the un-sharded kernel and with the fp32 oracle."""
+    _native_loaded()
+    from flash_attention_ipu_b200 import ring
+    import flash_attention_ipu.auto  # noqa: F401  (SDPA override = the un-sharded CUDA path)
+    torch.manual_seed(SEED)
+    B, H = 1, 2
+    q, k, v, dout = (torch.randn(B, H, T, D).bfloat16() for _ in range(4))
+    sh = lambda t: [ring.zigzag_shard(t.cuda(), r, world) for r in range(world)]
+    outs, grads = ring.ring_attention_emulated(sh(q), sh(k), sh(v), sh(dout))
+    torch.cuda.synchronize()
+    out = ring.zigzag_unshard(outs).float().cpu()
+    dq, dk, dv = (ring.zigzag_unshard([g[i] for g in grads]).float().cpu() for i in range(3))
+    # fp32 oracle on the same rounded inputs
+    qf, kf, vf = (t.float().requires_grad_(True) for t in (q, k, v))
+    ref = ao.sdpa_reference(qf, kf, vf, is_causal=True)
+    ref.backward(dout.float())
+    assert (out - ref.detach()).abs().max().item() <= 1e-2
+    for got, want in ((dq, qf.grad), (dk, kf.grad), (dv, vf.grad)):
+        assert rel_fro(got, want) <= 1e-2
+    # un-sharded CUDA kernel
+    qd, kd, vd = (t.cuda().requires_grad_(True) for t in (q, k, v))
+    o1 = torch.nn.functional.scaled_dot_product_attention(qd, kd, vd, is_causal=True)
+    o1.backward(dout.cuda())
+    assert (out - o1.detach().float().cpu()).abs().max().item() <= 1e-2
+    for got, want in ((dq, qd.grad), (dk, kd.grad), (dv, vd.grad)):
+        assert rel_fro(got, want.float().cpu()) <= 1e-2
