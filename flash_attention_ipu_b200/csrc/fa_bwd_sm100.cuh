@@ -29,10 +29,10 @@
 namespace fa {
 
 constexpr int kBwdThreads = 512;
-#ifndef FA_BWD_POLY_EVERY
-#define FA_BWD_POLY_EVERY 4
+#ifndef FA_BWD_POLY_PAIRS
+#define FA_BWD_POLY_PAIRS 12
 #endif
-constexpr int kBwdPolyEvery = FA_BWD_POLY_EVERY;  // every n-th pair of exponentials runs on the FMA pipe (0: none)
+constexpr int kBwdPolyPairs = FA_BWD_POLY_PAIRS;  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
 
 struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
@@ -325,19 +325,25 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tmem_ld32(tS + 32, s[1]);
         tmem_ld_wait();
         const uint64_t c2 = f2_pack(p.scale_log2, p.scale_log2);
-        #pragma unroll
-        for (int c = 0; c < 64; c += 2) {
-          float x0, x1;
-          f2_unpack(f2_fma(f2_pack(s[c >> 5][c & 31], s[c >> 5][(c & 31) + 1]), c2, f2_pack(nl[c], nl[c + 1])),
-                    x0, x1);
-          constexpr int kEvery = kBwdPolyEvery > 0 ? kBwdPolyEvery : 1;
-          if (kBwdPolyEvery > 0 && (c >> 1) % kEvery == kEvery - 1) {  // this pair on the FMA pipe
-            poly_exp2_pair(x0, x1, pr[c], pr[c + 1]);
-          } else {
-            pr[c] = fast_exp2(x0);
-            pr[c + 1] = fast_exp2(x1);
+        // kBwdPolyPairs of the 32 pairs run as a polynomial on the FMA pipe, the rest on MUFU; the
+        // two warpgroups (one warp of each per SM sub-partition) take the two kinds in opposite
+        // order so that one keeps the FMA pipe busy while the other occupies MUFU.
+        auto exp_all = [&](auto poly_first) {
+          #pragma unroll
+          for (int c = 0; c < 64; c += 2) {
+            float x0, x1;
+            f2_unpack(f2_fma(f2_pack(s[c >> 5][c & 31], s[c >> 5][(c & 31) + 1]), c2, f2_pack(nl[c], nl[c + 1])),
+                      x0, x1);
+            const int pair = c >> 1;
+            if (decltype(poly_first)::value ? pair < kBwdPolyPairs : pair >= 32 - kBwdPolyPairs) {
+              poly_exp2_pair(x0, x1, pr[c], pr[c + 1]);
+            } else {
+              pr[c] = fast_exp2(x0);
+              pr[c + 1] = fast_exp2(x1);
+            }
           }
-        }
+        };
+        if (wg) exp_all(BoolC<true>{}); else exp_all(BoolC<false>{});
       }
       // causal mask on tiles that cross the diagonal: query column visible iff key <= q + shift
       if (p.causal && j * 128 + 127 > i * 128 + p.shift) {

@@ -28,7 +28,10 @@ namespace fa {
 constexpr int kBlockM = 128;     // query rows per Q tile (= TMEM lanes)
 constexpr int kBlockN = 128;     // keys per KV tile
 constexpr int kFwdThreads = 384;
-constexpr int kKStages = 2;
+#ifndef FA_FWD_K_STAGES
+#define FA_FWD_K_STAGES 3
+#endif
+constexpr int kKStages = FA_FWD_K_STAGES;  // K ring depth (the TMA round trip is latency-, not bandwidth-bound)
 constexpr int kVStages = 2;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -59,7 +62,7 @@ struct FwdSmem {
   static constexpr int kNumBars = 2 + 2 * kKStages + 2 * kVStages + 2 + 2 + 2;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kBytes = kTmemPtrOff + 16;
-  static constexpr int kAlloc = kBytes + 1024;  // slack for manual 1024-B alignment
+  static constexpr int kAlloc = kBytes;  // the dynamic shared memory base is 1024-byte aligned (checked)
 };
 
 // number of KV tiles Q tile `t` must visit
@@ -80,9 +83,11 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                     const FwdParams p) {
   using L = FwdSmem<D>;
   constexpr int kHalves = D / 64;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                              ~static_cast<uintptr_t>(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) {
+    printf("fa_b200: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + L::kBarOff);
   uint64_t *q_full = bars;                       // [2]
   uint64_t *k_full = q_full + 2;                 // [kKStages]
@@ -167,19 +172,23 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const uint32_t a = q_lo + i * (L::kTileBytes >> 4);
         const uint32_t bb = k_lo + (j % kKStages) * (L::kTileBytes >> 4);
         const uint32_t d = tmem_base + i * 128;
+#ifndef FA_EXPERIMENT_FWD_NO_S  // timing experiments only (wrong results)
         #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
           const uint32_t off = ((k / 4) * L::kHalfBytes + (k % 4) * 32) >> 4;
           umma_ss2(d, a + off, hi, bb + off, hi, idesc_s, k > 0);
         }
+#endif
         umma_commit(&s_full[i]);
       };
       auto issue_pv = [&](int i, int j) {  // O_i += P_i V_j   (A = P in TMEM, B = V MN-major)
         const uint32_t bb = v_lo + (j % kVStages) * (L::kTileBytes >> 4);
         const uint32_t d = tmem_base + 256 + i * D, a = tmem_base + i * 128;
+#ifndef FA_EXPERIMENT_FWD_NO_PV
         #pragma unroll
         for (int k = 0; k < kBlockN / 16; ++k)
           umma_ts2(d, a + k * 8, bb + k * (2048 >> 4), hi, idesc_pv, (j > 0 || k > 0));
+#endif
       };
 
       mbar_wait(&q_full[0], 0);
@@ -236,6 +245,11 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     for (int j = 0; j < n; ++j) {
       mbar_wait(&s_full[i], j & 1);
       tc_fence_after();
+#ifdef FA_EXPERIMENT_FWD_NO_SOFTMAX
+      tc_fence_before();
+      mbar_arrive(&p_full[i]);
+      continue;
+#endif
       uint32_t sr[4][32];
       #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, sr[c]);
