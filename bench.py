@@ -215,8 +215,14 @@ def run_ours(args):
     bwd_tf = attention_flops(G, T, D, fwd=False) / (ms_bwd * 1e-3) / 1e12
     dominant = "bwd" if ms_bwd >= ms_fwd else "fwd"
     ach = bwd_tf if dominant == "bwd" else fwd_tf
+    traffic = None  # dram bytes read + written per launch of the dominant kernel, from the committed ncu capture
+    try:
+        tj = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text())[f"fa_{dominant}_sm100"]
+        traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    except Exception:
+        pass
     roofline = {"bound": "tensor", "kernel": f"fa_{dominant}_sm100", "achieved": ach, "peak": peak,
-                "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
                 "peak_kind": f"{peak_kind} cuBLAS bf16 sustained (burst {peaks['bf16_tflops']})",
                 "fwd_tflops": fwd_tf, "bwd_tflops": bwd_tf, "ms_fwd": ms_fwd, "ms_bwd": ms_bwd,
                 "frac_of_nominal_2250": value / world / 2250.0}
