@@ -33,6 +33,13 @@ constexpr int kFwdThreads = 384;
 #endif
 constexpr int kKStages = FA_FWD_K_STAGES;  // K ring depth (the TMA round trip is latency-, not bandwidth-bound)
 constexpr int kVStages = 2;
+#ifndef FA_FWD_P_SPLIT
+#define FA_FWD_P_SPLIT 2
+#endif
+// P_i is handed to the MMA warp in kPSplit column groups, so that O_i += P_i V_j starts on the first
+// keys while the exponentials of the last ones are still being computed (shortens the
+// S -> softmax -> PV dependency chain that bounds the kernel)
+constexpr int kPSplit = FA_FWD_P_SPLIT;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 #ifndef FA_FWD_POLY_EVERY
@@ -59,7 +66,7 @@ struct FwdSmem {
   static constexpr int kKOff = kQOff + 2 * kTileBytes;
   static constexpr int kVOff = kKOff + kKStages * kTileBytes;
   static constexpr int kBarOff = kVOff + kVStages * kTileBytes;
-  static constexpr int kNumBars = 2 + 2 * kKStages + 2 * kVStages + 2 + 2 + 2;
+  static constexpr int kNumBars = 2 + 2 * kKStages + 2 * kVStages + 2 + 2 * kPSplit + 2;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kBytes = kTmemPtrOff + 16;
   static constexpr int kAlloc = kBytes;  // the dynamic shared memory base is 1024-byte aligned (checked)
@@ -95,8 +102,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t *v_full = k_empty + kKStages;         // [kVStages]
   uint64_t *v_empty = v_full + kVStages;         // [kVStages]
   uint64_t *s_full = v_empty + kVStages;         // [2]  MMA -> softmax : S_i ready
-  uint64_t *p_full = s_full + 2;                 // [2]  softmax -> MMA : P_i ready (128 arrivals)
-  uint64_t *o_full = p_full + 2;                 // [2]  MMA -> softmax : final O_i ready
+  uint64_t *p_full = s_full + 2;                 // [2][kPSplit]  softmax -> MMA : part of P_i ready (128 arrivals)
+  uint64_t *o_full = p_full + 2 * kPSplit;               // [2]  MMA -> softmax : final O_i ready
   uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
 
   const int warp = uniform_warp_idx();
@@ -115,7 +122,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   if (warp == 9 && lane == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&q_full[i], 1); mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128);
+      mbar_init(&q_full[i], 1); mbar_init(&s_full[i], 1);
+      for (int q = 0; q < kPSplit; ++q) mbar_init(&p_full[i * kPSplit + q], 128);
       mbar_init(&o_full[i], 1);
     }
     for (int i = 0; i < kKStages; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
@@ -181,14 +189,24 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #endif
         umma_commit(&s_full[i]);
       };
-      auto issue_pv = [&](int i, int j) {  // O_i += P_i V_j   (A = P in TMEM, B = V MN-major)
+      // O_i += P_i V_j (A = P in TMEM, B = V MN-major), one group of key columns at a time as the
+      // softmax warps release them
+      auto issue_pv = [&](int i, int j, uint32_t parity) {
         const uint32_t bb = v_lo + (j % kVStages) * (L::kTileBytes >> 4);
         const uint32_t d = tmem_base + 256 + i * D, a = tmem_base + i * 128;
-#ifndef FA_EXPERIMENT_FWD_NO_PV
+        constexpr int kSteps = kBlockN / 16 / kPSplit;
         #pragma unroll
-        for (int k = 0; k < kBlockN / 16; ++k)
-          umma_ts2(d, a + k * 8, bb + k * (2048 >> 4), hi, idesc_pv, (j > 0 || k > 0));
+        for (int q = 0; q < kPSplit; ++q) {
+          mbar_wait(&p_full[i * kPSplit + q], parity);
+          tc_fence_after();
+#ifndef FA_EXPERIMENT_FWD_NO_PV
+          if (leader) {
+            #pragma unroll
+            for (int k = q * kSteps; k < (q + 1) * kSteps; ++k)
+              umma_ts2(d, a + k * 8, bb + k * (2048 >> 4), hi, idesc_pv, (j > 0 || k > 0));
+          }
 #endif
+        }
       };
 
       mbar_wait(&q_full[0], 0);
@@ -204,10 +222,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         if (j >= 1 && j - 1 < n1) {
           mbar_wait(&v_full[(j - 1) % kVStages], ((j - 1) / kVStages) & 1);
-          mbar_wait(&p_full[1], (j - 1) & 1);
-          tc_fence_after();
+          issue_pv(1, j - 1, (j - 1) & 1);
           if (leader) {
-            issue_pv(1, j - 1);
             umma_commit(&v_empty[(j - 1) % kVStages]);
             if (j - 1 == n1 - 1) umma_commit(&o_full[1]);
           }
@@ -218,10 +234,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         if (j < n0) {
           mbar_wait(&v_full[j % kVStages], (j / kVStages) & 1);
-          mbar_wait(&p_full[0], j & 1);
-          tc_fence_after();
+          issue_pv(0, j, j & 1);
           if (leader) {
-            issue_pv(0, j);
             if (!(j < n1)) umma_commit(&v_empty[j % kVStages]);
             if (j == n0 - 1) umma_commit(&o_full[0]);
           }
@@ -247,7 +261,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tc_fence_after();
 #ifdef FA_EXPERIMENT_FWD_NO_SOFTMAX
       tc_fence_before();
-      mbar_arrive(&p_full[i]);
+      for (int q = 0; q < kPSplit; ++q) mbar_arrive(&p_full[i * kPSplit + q]);
       continue;
 #endif
       uint32_t sr[4][32];
@@ -273,7 +287,11 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int c = 0; c < 4; ++c)
         #pragma unroll
         for (int e = 0; e < 32; e += 2)
+#ifndef FA_EXPERIMENT_FWD_NO_MAX
           mx4[(e >> 1) & 3] = fmax3(mx4[(e >> 1) & 3], __uint_as_float(sr[c][e]), __uint_as_float(sr[c][e + 1]));
+#else
+          if (e == 0) mx4[c] = __uint_as_float(sr[c][0]);
+#endif
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = mx * p.scale_log2;
 
@@ -312,13 +330,30 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             if (decltype(use_poly)::value && kFwdPolyEvery > 0 && (e >> 1) % kEvery == kEvery - 1) {
               poly_exp2_pair(x0, x1, p0, p1);
             } else {
+#ifndef FA_EXPERIMENT_FWD_NO_EXP
               p0 = fast_exp2(x0);
               p1 = fast_exp2(x1);
+#else
+              p0 = x0; p1 = x1;
+#endif
             }
             sum2[(e >> 1) & 3] = f2_add(sum2[(e >> 1) & 3], f2_pack(p0, p1));
+#ifndef FA_EXPERIMENT_FWD_NO_PACK
             pk[e >> 1] = pack2<kBf16>(p0, p1);
+#else
+            if ((e >> 1) < 2) pk[e >> 1] = __float_as_uint(p0 + p1);
+#endif
           }
+#ifndef FA_EXPERIMENT_FWD_NO_PACK
           tmem_st16(tS + c * 16, pk);
+#else
+          asm volatile("" ::"r"(pk[0]), "r"(pk[1]));
+#endif
+          if ((c + 1) % (4 / kPSplit) == 0) {  // this group of P columns is complete: release it
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&p_full[i * kPSplit + (c + 1) / (4 / kPSplit) - 1]);
+          }
         }
       };
       if (tile_masked) exp_tile(BoolC<false>{}); else exp_tile(BoolC<true>{});
@@ -328,9 +363,6 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         (void)b0; (void)b1;
         l += a0 + a1;
       }
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(&p_full[i]);
     }
 
     // ---------------- epilogue: O_i / l -> smem (SW128) -> TMA store ; LSE ----------------
