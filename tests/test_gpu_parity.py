@@ -284,3 +284,22 @@ def test_emulated_ring_vs_single_gpu_and_oracle(world, T, D):
     assert (out - o1.detach().float().cpu()).abs().max().item() <= 1e-2
     for got, want in ((dq, qd.grad), (dk, kd.grad), (dv, vd.grad)):
         assert rel_fro(got, want.float().cpu()) <= 1e-2
+
+
+def test_nanogpt_demo_loss_curve_parity():
+    """SURVEY.md 8f-2 / notebook Appendix A of the reference: training the nanoGPT-shaped model with
+    the SDPA override follows the un-patched loss curve (same seed, bf16 autocast), the loss goes
+    down, and the attention launches really are ours."""
+    import importlib.util
+    import pathlib
+    spec = importlib.util.spec_from_file_location(
+        "train_nanogpt_b200", pathlib.Path(__file__).resolve().parent.parent / "demo" / "train_nanogpt_b200.py")
+    demo = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(demo)
+    kw = dict(steps=40, n_layer=2, batch=16, block=256, n_head=6, n_embd=384)
+    base, _, l0 = demo.train(False, **kw)
+    ours, _, l1 = demo.train(True, **kw)
+    assert l0 == 0 and l1 >= 2 * 2 * 40          # fwd + bwd (+ prep/convert) per layer per step
+    assert ours[-1] < ours[0] - 0.5               # it learns
+    assert max(abs(a - b) for a, b in zip(base[:10], ours[:10])) <= 0.02   # same curve while chaos is small
+    assert abs(sum(base[-10:]) - sum(ours[-10:])) / 10 <= 0.1
