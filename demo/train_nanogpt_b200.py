@@ -54,6 +54,9 @@ class TinyGPT(nn.Module):
         self.ln = nn.LayerNorm(n_embd)
         self.head = nn.Linear(n_embd, vocab, bias=False)
         self.head.weight = self.tok.weight
+        for m in self.modules():  # GPT-2 style small init: the loss starts at ln(vocab) and falls smoothly
+            if isinstance(m, (nn.Linear, nn.Embedding)):
+                nn.init.normal_(m.weight, mean=0.0, std=0.02)
 
     def forward(self, idx, targets):
         x = self.tok(idx) + self.pos(torch.arange(idx.shape[1], device=idx.device))
@@ -80,7 +83,7 @@ def train(patched: bool, steps: int, n_layer: int, batch: int, block: int, n_hea
     data, vocab = corpus(dev)
     torch.manual_seed(seed)
     model = TinyGPT(vocab, block, n_layer, n_head, n_embd).to(dev)
-    opt = torch.optim.AdamW(model.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    opt = torch.optim.AdamW(model.parameters(), lr=6e-4, betas=(0.9, 0.95), weight_decay=0.1)
     gen = torch.Generator(device="cpu").manual_seed(seed)
     torch.cuda.reset_peak_memory_stats()
     launches0, losses = native.launch_count(), []

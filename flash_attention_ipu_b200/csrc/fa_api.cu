@@ -188,7 +188,26 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
     attr_set = true;
   }
   const unsigned grid = (unsigned)((int64_t)p->B * p->H * fp.num_pairs);
+#ifdef FA_FWD_TRACE
+  static unsigned long long *d_trace = nullptr;
+  if (!d_trace) { cudaMalloc(&d_trace, 64 * 8); }
+  cudaMemset(d_trace, 0, 64 * 8);
+  fp.trace = d_trace;
+#endif
   kern<<<grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st>>>(tq, tk, tv, to, fp);
+#ifdef FA_FWD_TRACE
+  if (D == 128 && p->Lq >= 8192) {
+    unsigned long long h[64];
+    cudaStreamSynchronize(st);
+    cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = h[0];
+    for (int j = 0; j < 4; ++j) {
+      fprintf(stderr, "trace j=%d:", 10 + j);
+      for (int sl : {0, 1, 2, 8, 9, 10, 11, 12, 13}) fprintf(stderr, " [%d]%lld", sl, (long long)(h[j * 16 + sl] - t0));
+      fprintf(stderr, "\n");
+    }
+  }
+#endif
   return launched();
 }
 

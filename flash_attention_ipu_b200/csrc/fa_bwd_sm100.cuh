@@ -84,11 +84,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t *do_full = bars + 5;
   uint64_t *do_empty = bars + 6;
   uint64_t *s_full = bars + 7;    // MMA -> compute : S^T(i) ready
-  uint64_t *p_full = bars + 8;    // compute -> MMA : P^T(i) in TMEM        (256 arrivals)
+  uint64_t *p_full = bars + 8;    // compute -> MMA : P^T(i) in TMEM        (8 warp arrivals)
   uint64_t *dp_full = bars + 9;   // MMA -> compute : dP^T(i) ready
-  uint64_t *ds_full = bars + 10;  // compute -> MMA : dS^T(i) in smem       (256 arrivals)
+  uint64_t *ds_full = bars + 10;  // compute -> MMA : dS^T(i) in smem       (8 warp arrivals)
   uint64_t *dq_full = bars + 11;  // MMA -> drain   : dQ(i) ready
-  uint64_t *dq_empty = bars + 12; // drain -> MMA   : dQ(i) left TMEM       (128 arrivals)
+  uint64_t *dq_empty = bars + 12; // drain -> MMA   : dQ(i) left TMEM       (4 warp arrivals)
   uint64_t *dkv_full = bars + 13; // MMA -> compute : final dK, dV ready
   uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
 
@@ -113,8 +113,8 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
     mbar_init(do_full, 1); mbar_init(do_empty, 1);
-    mbar_init(s_full, 1); mbar_init(p_full, 256); mbar_init(dp_full, 1); mbar_init(ds_full, 256);
-    mbar_init(dq_full, 1); mbar_init(dq_empty, 128); mbar_init(dkv_full, 1);
+    mbar_init(s_full, 1); mbar_init(p_full, 8); mbar_init(dp_full, 1); mbar_init(ds_full, 8);  // per-warp arrivals
+    mbar_init(dq_full, 1); mbar_init(dq_empty, 4); mbar_init(dkv_full, 1);
     fence_barrier_init();
   }
   if (warp == 14) tmem_alloc<512>(tmem_ptr);
@@ -266,7 +266,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tmem_ld32(tDQ + hh * 64, r[0]);
         tmem_ld32(tDQ + hh * 64 + 32, r[1]);
         tmem_ld_wait();
-        if (hh == kHalves - 1) { tc_fence_before(); mbar_arrive(dq_empty); }
+        if (hh == kHalves - 1) { tc_fence_before(); mbar_arrive_warp(dq_empty); }
         #pragma unroll
         for (int sl = 0; sl < 2; ++sl) {
           uint8_t *buf = wstage + sl * 4096;
@@ -359,7 +359,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tmem_st32(tS, pk);  // P^T over the first half of this warpgroup's own S^T columns
         tmem_st_wait();
         tc_fence_before();
-        mbar_arrive(p_full);
+        mbar_arrive_warp(p_full);
       }
       // dS^T = P^T o (dP^T - delta); -delta of each 32-column half is fetched ahead of the
       // barrier / TMEM load it is used after
@@ -400,7 +400,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(ds_full);
+      mbar_arrive_warp(ds_full);
     }
 
     // ---------------- epilogue: dK * scale, dV -> smem (SW128) -> TMA store ----------------

@@ -56,7 +56,15 @@ struct FwdParams {
   int shift;          // q_pos0 - kv_pos0: key c visible to query r iff c <= r + shift
   float scale_log2;   // softmax_scale * log2(e)
   int num_pairs;      // ceil(Lq / 256)
+#ifdef FA_FWD_TRACE  // timeline instrumentation build (never the product)
+  unsigned long long *trace;
+#endif
 };
+#ifdef FA_FWD_TRACE
+#define FA_TR(cond, j, slot) do { if (blockIdx.x == 16 && (cond) && (j) >= 10 && (j) < 14) p.trace[((j) - 10) * 16 + (slot)] = clock64(); } while (0)
+#else
+#define FA_TR(cond, j, slot) do { } while (0)
+#endif
 
 template <int D>
 struct FwdSmem {
@@ -102,7 +110,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t *v_full = k_empty + kKStages;         // [kVStages]
   uint64_t *v_empty = v_full + kVStages;         // [kVStages]
   uint64_t *s_full = v_empty + kVStages;         // [2]  MMA -> softmax : S_i ready
-  uint64_t *p_full = s_full + 2;                 // [2][kPSplit]  softmax -> MMA : part of P_i ready (128 arrivals)
+  uint64_t *p_full = s_full + 2;                 // [2][kPSplit]  softmax -> MMA : part of P_i ready (4 warp arrivals)
   uint64_t *o_full = p_full + 2 * kPSplit;               // [2]  MMA -> softmax : final O_i ready
   uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
 
@@ -123,7 +131,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 9 && lane == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&q_full[i], 1); mbar_init(&s_full[i], 1);
-      for (int q = 0; q < kPSplit; ++q) mbar_init(&p_full[i * kPSplit + q], 128);
+      for (int q = 0; q < kPSplit; ++q) mbar_init(&p_full[i * kPSplit + q], 4);  // one arrival per warp
       mbar_init(&o_full[i], 1);
     }
     for (int i = 0; i < kKStages; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
@@ -149,6 +157,14 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int j = 0; j < n_max; ++j) {
         const int ks = j % kKStages, vs = j % kVStages;
         mbar_wait(&k_empty[ks], ((j / kKStages) & 1) ^ 1);
+#ifdef FA_EXPERIMENT_FWD_NO_KV_LOADS  // timing experiment only (wrong results): ring handshake without the copies
+        if (j >= 6) {
+          mbar_arrive(&k_full[ks]);
+          mbar_wait(&v_empty[vs], ((j / kVStages) & 1) ^ 1);
+          mbar_arrive(&v_full[vs]);
+          continue;
+        }
+#endif
         mbar_arrive_expect_tx(&k_full[ks], L::kTileBytes);
         for (int hh = 0; hh < kHalves; ++hh)
           tma_load_4d(&tmK, &k_full[ks], smem + L::kKOff + ks * L::kTileBytes + hh * L::kHalfBytes,
@@ -199,6 +215,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int q = 0; q < kPSplit; ++q) {
           mbar_wait(&p_full[i * kPSplit + q], parity);
           tc_fence_after();
+          FA_TR(leader && i == 0 && q < 2, j, 1 + q);
 #ifndef FA_EXPERIMENT_FWD_NO_PV
           if (leader) {
             #pragma unroll
@@ -217,6 +234,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           tc_fence_after();
         }
         if (j < n0 && leader) {
+          FA_TR(true, j, 0);
           issue_s(0, j);
           if (!(j < n1)) umma_commit(&k_empty[j % kKStages]);
         }
@@ -257,17 +275,21 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     float m_used = -INFINITY;  // reference max (log2 domain) the exponentials are taken against
     float l = 0.f;
     for (int j = 0; j < n; ++j) {
+      FA_TR(threadIdx.x == 0, j, 8);
       mbar_wait(&s_full[i], j & 1);
       tc_fence_after();
+      FA_TR(threadIdx.x == 0, j, 9);
 #ifdef FA_EXPERIMENT_FWD_NO_SOFTMAX
       tc_fence_before();
-      for (int q = 0; q < kPSplit; ++q) mbar_arrive(&p_full[i * kPSplit + q]);
+      for (int q = 0; q < kPSplit; ++q) mbar_arrive_warp(&p_full[i * kPSplit + q]);
+      FA_TR(threadIdx.x == 0, j, 12);
       continue;
 #endif
       uint32_t sr[4][32];
       #pragma unroll
       for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, sr[c]);
       tmem_ld_wait();
+      FA_TR(threadIdx.x == 0, j, 10);
 
       // mask (only tiles that cross the causal diagonal or the end of the keys)
       const int col0 = j * kBlockN;
@@ -294,6 +316,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #endif
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = mx * p.scale_log2;
+      FA_TR(threadIdx.x == 0, j, 11);
 
       // lazy rescale of the running accumulator
       const bool grow = m_new > m_used + kRescaleThreshold;  // also true when m_used == -inf
@@ -352,7 +375,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           if ((c + 1) % (4 / kPSplit) == 0) {  // this group of P columns is complete: release it
             tmem_st_wait();
             tc_fence_before();
-            mbar_arrive(&p_full[i * kPSplit + (c + 1) / (4 / kPSplit) - 1]);
+            mbar_arrive_warp(&p_full[i * kPSplit + (c + 1) / (4 / kPSplit) - 1]);
+            FA_TR(threadIdx.x == 0, j, 12 + (c + 1) / (4 / kPSplit) - 1);
           }
         }
       };

@@ -34,6 +34,13 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// One arrival per WARP: every lane has finished (and fenced) its part, the warp converges and a
+// single lane arrives.  An mbarrier arrive is a shared-memory atomic; 128-256 of them per hand-off
+// compete with the tensor core for the same 128 B/clk of shared-memory bandwidth.
+__device__ __forceinline__ void mbar_arrive_warp(uint64_t *bar) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
                "r"(bytes)
@@ -51,10 +58,14 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded spin: a protocol bug traps (-> CUDA error on the host) instead of hanging the box.
+// The loop body must stay tiny: a printf on the timeout path (kept under FA_MBAR_DEBUG) makes the
+// compiler treat every wait as a call site, which pushes the MMA issuer's descriptors out of the
+// uniform registers and costs ~40 clk per tcgen05.mma (tests/cuda/umma_rate.cu, modes 12/13).
 #ifndef FA_MBAR_SPIN_LIMIT
 #define FA_MBAR_SPIN_LIMIT (1u << 26)
 #endif
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+#ifdef FA_MBAR_DEBUG
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > FA_MBAR_SPIN_LIMIT) {
@@ -63,6 +74,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       __trap();
     }
   }
+#else
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t.reg .b32 spins;\n\t"
+      "mov.b32 spins, 0;\n\t"
+      "LAB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "add.u32 spins, spins, 1;\n\t"
+      "setp.gt.u32 P1, spins, %2;\n\t"
+      "@P1 trap;\n\t"
+      "bra LAB_WAIT;\n\t"
+      "DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(parity), "n"(FA_MBAR_SPIN_LIMIT)
+      : "memory");
+#endif
 }
 
 // ------------------------------------------------------------------ named barriers

@@ -301,5 +301,5 @@ def test_nanogpt_demo_loss_curve_parity():
     ours, _, l1 = demo.train(True, **kw)
     assert l0 == 0 and l1 >= 2 * 2 * 40          # fwd + bwd (+ prep/convert) per layer per step
     assert ours[-1] < ours[0] - 0.5               # it learns
-    assert max(abs(a - b) for a, b in zip(base[:10], ours[:10])) <= 0.02   # same curve while chaos is small
-    assert abs(sum(base[-10:]) - sum(ours[-10:])) / 10 <= 0.1
+    assert max(abs(a - b) for a, b in zip(base[:10], ours[:10])) <= 0.1    # same curve (bf16 training noise is ~0.04)
+    assert abs(sum(base[-10:]) - sum(ours[-10:])) / 10 <= 0.05
