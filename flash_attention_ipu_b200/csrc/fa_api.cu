@@ -190,20 +190,20 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const unsigned grid = (unsigned)((int64_t)p->B * p->H * fp.num_pairs);
 #ifdef FA_FWD_TRACE
   static unsigned long long *d_trace = nullptr;
-  if (!d_trace) { cudaMalloc(&d_trace, 64 * 8); }
-  cudaMemset(d_trace, 0, 64 * 8);
+  if (!d_trace) { cudaMalloc(&d_trace, 128 * 8); }
+  cudaMemset(d_trace, 0, 128 * 8);
   fp.trace = d_trace;
 #endif
   kern<<<grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st>>>(tq, tk, tv, to, fp);
 #ifdef FA_FWD_TRACE
   if (D == 128 && p->Lq >= 8192) {
-    unsigned long long h[64];
+    unsigned long long h[128];
     cudaStreamSynchronize(st);
     cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);
     const unsigned long long t0 = h[0];
     for (int j = 0; j < 4; ++j) {
       fprintf(stderr, "trace j=%d:", 10 + j);
-      for (int sl : {0, 1, 2, 8, 9, 10, 11, 12, 13}) fprintf(stderr, " [%d]%lld", sl, (long long)(h[j * 16 + sl] - t0));
+      for (int sl : {16, 0, 17, 18, 19, 20, 21, 1, 2, 22, 9, 12}) fprintf(stderr, " [%d]%lld", sl, (long long)(h[j * 32 + sl] - t0));
       fprintf(stderr, "\n");
     }
   }

@@ -61,7 +61,7 @@ struct FwdParams {
 #endif
 };
 #ifdef FA_FWD_TRACE
-#define FA_TR(cond, j, slot) do { if (blockIdx.x == 16 && (cond) && (j) >= 10 && (j) < 14) p.trace[((j) - 10) * 16 + (slot)] = clock64(); } while (0)
+#define FA_TR(cond, j, slot) do { if (blockIdx.x == 16 && (cond) && (j) >= 10 && (j) < 14) p.trace[((j) - 10) * 32 + (slot)] = clock64(); } while (0)
 #else
 #define FA_TR(cond, j, slot) do { } while (0)
 #endif
@@ -229,6 +229,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       mbar_wait(&q_full[0], 0);
       mbar_wait(&q_full[1], 0);
       for (int j = 0; j <= n_max; ++j) {
+        FA_TR(leader, j, 16);
         if (j < n_max) {
           mbar_wait(&k_full[j % kKStages], (j / kKStages) & 1);
           tc_fence_after();
@@ -237,10 +238,13 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           FA_TR(true, j, 0);
           issue_s(0, j);
           if (!(j < n1)) umma_commit(&k_empty[j % kKStages]);
+          FA_TR(true, j, 17);
         }
         if (j >= 1 && j - 1 < n1) {
           mbar_wait(&v_full[(j - 1) % kVStages], ((j - 1) / kVStages) & 1);
+          FA_TR(leader, j, 18);
           issue_pv(1, j - 1, (j - 1) & 1);
+          FA_TR(leader, j, 19);
           if (leader) {
             umma_commit(&v_empty[(j - 1) % kVStages]);
             if (j - 1 == n1 - 1) umma_commit(&o_full[1]);
@@ -249,10 +253,13 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (j < n1 && leader) {
           issue_s(1, j);
           umma_commit(&k_empty[j % kKStages]);
+          FA_TR(true, j, 20);
         }
         if (j < n0) {
           mbar_wait(&v_full[j % kVStages], (j / kVStages) & 1);
+          FA_TR(leader, j, 21);
           issue_pv(0, j, j & 1);
+          FA_TR(leader, j, 22);
           if (leader) {
             if (!(j < n1)) umma_commit(&v_empty[j % kVStages]);
             if (j == n0 - 1) umma_commit(&o_full[0]);

@@ -20,11 +20,11 @@ __device__ __forceinline__ void mbar_wait_lean(uint64_t *bar, uint32_t parity) {
 }
 
 template <int mode>
-__global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long *out, int random_data) {
+__global__ void __launch_bounds__(384, 1) rate_kernel(int iters, long long *out, int random_data) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar, bar2[4];
   __shared__ uint32_t tmem_ptr;
-  for (int i = threadIdx.x; i < 128 * 1024 / 4; i += 128) {
+  for (int i = threadIdx.x; i < 128 * 1024 / 4; i += blockDim.x) {
     // zeros, or pseudo-random bf16 pairs in (-2, 2): real operand bit patterns toggle the datapath
     uint32_t x = (i * 2654435761u) ^ (i >> 7) * 40503u, y = x * 2246822519u + 374761393u;
     const uint32_t v = ((x & 0x807f807fu) | 0x3f003f00u) ^ (y & 0x00800080u);
@@ -37,7 +37,10 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long *out,
   __syncthreads();
   tc_fence_after();
   const uint32_t tm = tmem_ptr;
-  const bool warp_mode = mode >= 11;
+  if (mode >= 19 && threadIdx.x >= 32) {  // bystander warps polling an mbarrier, like idle pipeline roles
+    mbar_wait_lean(&bar2[2], 0);
+  }
+  const bool warp_mode = mode >= 11;  // smem: A at 0, B ring of 3 x 32 KB at 32 KB
   const bool leader = warp_mode ? (threadIdx.x < 32 && elect_one()) : threadIdx.x == 0;
   if (warp_mode ? threadIdx.x < 32 : threadIdx.x == 0) {
     constexpr uint32_t hi = smem_desc_hi(1024);
@@ -50,11 +53,15 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long *out,
     for (int it = 0; it < iters; ++it) {
       if (mode == 11 || mode == 12) tc_fence_after();
       if (mode == 12) { mbar_wait(&bar2[3], 1); }       // a wait that is already satisfied (bounded-spin form)
-      if (mode == 13) { mbar_wait_lean(&bar2[3], 1); }  // the same wait, lean form
-      if (leader) {
+      if (mode == 13 || mode == 14) { mbar_wait_lean(&bar2[3], 1); }  // the same wait, lean form
+      if (mode == 15) { mbar_wait_lean(&bar2[3], 1); tc_fence_after(); }
+      if (mode == 16) { mbar_wait_lean(&bar2[3], 1); mbar_wait_lean(&bar2[1], 1); mbar_wait_lean(&bar2[3], 1); mbar_wait_lean(&bar2[1], 1); }
+      const uint32_t stage = (mode >= 17) ? static_cast<uint32_t>((it >> 1) % 3) * (32768 >> 4) : 0u;  // ring stage
+      if (mode >= 18) { mbar_wait_lean(&bar2[3], 1); tc_fence_after(); }
+      if (leader && (mode < 14 || mode >= 17)) {  // mode 19: as 18 with 11 bystander warps
       #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const uint32_t offk = ((k / 4) * 16384 + (k % 4) * 32) >> 4, offmn = k * (2048 >> 4);
+        const uint32_t offk = (((k / 4) * 16384 + (k % 4) * 32) >> 4) + stage, offmn = k * (2048 >> 4) + stage;
         switch (mode) {
           case 0: umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, 1); break;             // S = Q K^T
           case 1: umma_ts2(tm + 256, tm + k * 8, b_mn + offmn, hi, i_kmn, 1); break;         // O += P V
@@ -64,18 +71,19 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, long long *out,
           case 5: umma_ss2(tm, a_k + offk, hi, b_mn + offmn, hi, i_kmn, 1); break;           // dK = dS^T Q
           case 6: umma_ts2(tm + 256, tm + k * 8, b_k + offk, hi, i_kk, 1); break;            // TS, B K-major
           case 8: case 10: umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, 1); break;     // + commits
-          case 9: case 7: case 11: case 12: case 13: if (it & 1) umma_ts2(tm + 256, tm + k * 8, b_mn + offmn, hi, i_kmn, 1);    // fwd mix
+          case 9: case 7: case 11: case 12: case 13: case 17: case 18: case 19: if (it & 1) umma_ts2(tm + 256, tm + k * 8, b_mn + offmn, hi, i_kmn, 1);    // fwd mix
                   else umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, 1); break;
         }
         if (mode == 10 && k == 3) umma_commit(&bar2[1]);
       }
-      if (mode >= 8) umma_commit(&bar2[it & 1 ? 2 : 0]);   // one commit per 8 MMAs, nobody waits on it
+      if (mode >= 8) umma_commit(&bar2[mode >= 19 ? 0 : (it & 1 ? 2 : 0)]);   // one commit per 8 MMAs, nobody waits on it
       }
       if (warp_mode) __syncwarp();
     }
     if (leader) umma_commit(&bar);
     mbar_wait(&bar, 0);
     if (leader) out[blockIdx.x] = clock64() - t0;
+    if (mode >= 19 && leader) mbar_arrive(&bar2[2]);  // release the bystanders
   }
   tc_fence_before();
   __syncthreads();
@@ -90,21 +98,26 @@ int main() {
                          "mode 0 + tcgen05.commit every 8 MMAs", "mode 7 + tcgen05.commit every 8 MMAs",
                          "mode 0 + tcgen05.commit every 4 MMAs",
                          "warp loop, mode 9 + tcgen05.fence::after_thread_sync per GEMM", "warp loop, mode 11 + satisfied mbarrier wait per GEMM",
-                         "warp loop, mode 9 + satisfied mbarrier wait per GEMM"};
-  const int nominal[] = {64, 64, 64, 128, 32, 64, 64, 64, 64, 64, 64, 64, 64, 64};
+                         "warp loop, mode 9 + satisfied mbarrier wait per GEMM",
+                         "NO MMAs: one satisfied mbarrier wait per iteration (clk per 8 = per wait / 8)",
+                         "NO MMAs: satisfied wait + tcgen05.fence::after per iteration", "NO MMAs: 4 satisfied waits per iteration",
+                         "warp loop, forward mix, B descriptor changes every GEMM (ring stage) + commit", "mode 17 + satisfied wait + fence per GEMM",
+                         "mode 18 + 11 bystander warps spinning on mbarrier.try_wait"};
+  const int nominal[] = {64, 64, 64, 128, 32, 64, 64, 64, 64, 64, 64, 64, 64, 64, 0, 0, 0, 64, 64, 64};
   long long *d, h[148];
   cudaMalloc(&d, sizeof(h));
   const int iters = 512;
-  void (*kerns[14])(int, long long *, int) = {rate_kernel<0>, rate_kernel<1>, rate_kernel<2>, rate_kernel<3>,
+  void (*kerns[20])(int, long long *, int) = {rate_kernel<0>, rate_kernel<1>, rate_kernel<2>, rate_kernel<3>,
                                         rate_kernel<4>, rate_kernel<5>, rate_kernel<6>, rate_kernel<7>,
                                         rate_kernel<8>, rate_kernel<9>, rate_kernel<10>,
-                                        rate_kernel<11>, rate_kernel<12>, rate_kernel<13>};
+                                        rate_kernel<11>, rate_kernel<12>, rate_kernel<13>,
+                                        rate_kernel<14>, rate_kernel<15>, rate_kernel<16>, rate_kernel<17>, rate_kernel<18>, rate_kernel<19>};
   for (int rnd = 0; rnd < 2; ++rnd)
-  for (int mode = 0; mode < 14; ++mode) {
+  for (int mode = 0; mode < 20; ++mode) {
     if (rnd && mode != 0 && mode != 1 && mode != 7) continue;
     if (rnd) printf("random operand data: ");
     cudaFuncSetAttribute(kerns[mode], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    kerns[mode]<<<148, 128, 200 * 1024>>>(iters * (rnd ? 8 : 1), d, rnd);
+    kerns[mode]<<<148, mode >= 19 ? 384 : 128, 200 * 1024>>>(iters * (rnd ? 8 : 1), d, rnd);
     if (cudaDeviceSynchronize() != cudaSuccess) { printf("mode %d: CUDA error %s\n", mode, cudaGetErrorString(cudaGetLastError())); return 1; }
     cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
     double s = 0; long long mx = 0;
