@@ -227,14 +227,14 @@ def run_ours(args):
                 "fwd_tflops": fwd_tf, "bwd_tflops": bwd_tf, "ms_fwd": ms_fwd, "ms_bwd": ms_bwd,
                 "frac_of_nominal_2250": value / world / 2250.0}
 
-    # ---- e2e: same public API, inputs start in pinned host memory, results end there
+    # ---- e2e: same public API, inputs start in pinned host memory, results end there.  The step
+    # is pipelined over chunks of (batch, head) groups (flash_attention_ipu_b200/streaming.py):
+    # upload of chunk c+1 and download of chunk c-1 overlap the attention of chunk c.
+    from flash_attention_ipu_b200.streaming import HostStreamedAttention
+    pipe = HostStreamedAttention(G, T, D, torch.bfloat16, dev, groups_per_chunk=8, num_chunks_q=ncq, num_chunks_kv=nckv)
+
     def e2e_step():
-        x = h_qkv.to(dev, non_blocking=True).requires_grad_(True)
-        g = h_do.to(dev, non_blocking=True)
-        out = fa.flash_attention_qkv_packed(x, ncq, nckv)
-        out.backward(g)
-        h_out.copy_(out.detach(), non_blocking=True)
-        h_dqkv.copy_(x.grad, non_blocking=True)
+        pipe.run(h_qkv, h_do, h_out, h_dqkv)
 
     e2e_step()
     barrier()

@@ -303,3 +303,28 @@ def test_nanogpt_demo_loss_curve_parity():
     assert ours[-1] < ours[0] - 0.5               # it learns
     assert max(abs(a - b) for a, b in zip(base[:10], ours[:10])) <= 0.1    # same curve (bf16 training noise is ~0.04)
     assert abs(sum(base[-10:]) - sum(ours[-10:])) / 10 <= 0.05
+
+
+def test_host_streamed_attention_matches_device_path():
+    """flash_attention_ipu_b200/streaming.py (what bench.py's e2e leg calls): chunked, overlapped
+    host->device->host pipeline gives exactly the result of the one-shot device call."""
+    import flash_attention_ipu as fa
+    from flash_attention_ipu_b200.streaming import HostStreamedAttention
+    torch.manual_seed(SEED)
+    G, L, D = 12, 384, 128
+    h_qkv = torch.randn(3, G, L, D).bfloat16().pin_memory()
+    h_do = torch.randn(G, L, D).bfloat16().pin_memory()
+    h_out = torch.empty(G, L, D, dtype=torch.bfloat16).pin_memory()
+    h_dqkv = torch.empty(3, G, L, D, dtype=torch.bfloat16).pin_memory()
+    pipe = HostStreamedAttention(G, L, D, groups_per_chunk=4)
+    for _ in range(2):  # second run re-uses the staging buffers
+        pipe.run(h_qkv, h_do, h_out, h_dqkv)
+    torch.cuda.synchronize()
+    x = h_qkv.cuda().requires_grad_(True)
+    out = fa.flash_attention_qkv_packed(x, 1, 1)
+    out.backward(h_do.cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(h_out, out.detach().cpu())
+    # dQ accumulates by fp32 atomics in a different order per launch: equal up to that
+    assert (h_dqkv.float() - x.grad.float().cpu()).abs().max().item() <= 2e-2
+    assert torch.equal(h_dqkv[1:], x.grad[1:].cpu())
