@@ -68,10 +68,18 @@ class ClockSampler(threading.Thread):
         except Exception:
             pass
 
-    def summary(self):
+    def mark(self):
+        """Index of the next sample: call at the start and the end of the timed region."""
+        return len(self.samples)
+
+    def summary(self, lo=0, hi=None):
+        """Median SM clock / throttle reasons over samples[lo:hi] (the timed region; the sampler is
+        started earlier so that nvidia-smi is already running when the region begins)."""
         if self.proc is not None:
             self.proc.terminate()
         self.join(timeout=6)
+        window = self.samples[lo:hi] if len(self.samples[lo:hi]) >= 3 else self.samples
+        self.samples = window
         mhz = sorted(int(s[0]) for s in self.samples if len(s) >= 7 and s[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for s in self.samples if len(s) >= 7 for n, v in zip(names, s[3:7]) if v == "Active"})
@@ -177,14 +185,16 @@ def run_ours(args):
     launches0 = native.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     barrier()
+    m0 = sampler.mark()
     ev[0].record()
     for _ in range(args.steps):
         step()
     ev[1].record()
     barrier()
+    m1 = sampler.mark()
     ms_total = ev[0].elapsed_time(ev[1])
     launches = native.launch_count() - launches0
-    clocks = sampler.summary()
+    clocks = sampler.summary(m0, m1)
     if world > 1:
         t = torch.tensor([ms_total], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -315,11 +325,13 @@ def run_ring(args):
     launches0 = native.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     barrier()
+    m0 = sampler.mark()
     ev[0].record()
     for _ in range(args.steps):
         step()
     ev[1].record()
     barrier()
+    m1 = sampler.mark()
     t = torch.tensor([ev[0].elapsed_time(ev[1])], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = t.item() / args.steps
@@ -332,7 +344,7 @@ def run_ring(args):
                    "parallelism": f"sequence sharded zig-zag over {world} GPU(s); ring KV exchange by NCCL P2P "
                                   f"({2 * B * H * L2 * D * 2} B per hop per rank) + fp32 LSE merge",
                    "l2": "per-rank K/V shards larger than L2 for world<=8"},
-        "clocks": sampler.summary(), "gpu_launches": native.launch_count() - launches0,
+        "clocks": sampler.summary(m0, m1), "gpu_launches": native.launch_count() - launches0,
     }
     if rank == 0:
         print(json.dumps(line), flush=True)

@@ -32,7 +32,10 @@ constexpr int kFwdThreads = 384;
 #define FA_FWD_K_STAGES 3
 #endif
 constexpr int kKStages = FA_FWD_K_STAGES;  // K ring depth (the TMA round trip is latency-, not bandwidth-bound)
-constexpr int kVStages = 2;
+#ifndef FA_FWD_V_STAGES
+#define FA_FWD_V_STAGES 2
+#endif
+constexpr int kVStages = FA_FWD_V_STAGES;
 #ifndef FA_FWD_P_SPLIT
 #define FA_FWD_P_SPLIT 2
 #endif
