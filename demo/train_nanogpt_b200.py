@@ -78,6 +78,7 @@ def train(patched: bool, steps: int, n_layer: int, batch: int, block: int, n_hea
     """One training run; returns (losses, peak_bytes, attention kernel launches)."""
     from flash_attention_ipu_b200._impl import native
     from flash_attention_ipu_b200._impl import scaled_dot_product_attention as sd  # importing it patches
+    was_patched = hasattr(F.scaled_dot_product_attention, "__wrapped__")
     (sd.install if patched else sd.uninstall)()
     dev = torch.device("cuda")
     data, vocab = corpus(dev)
@@ -98,7 +99,7 @@ def train(patched: bool, steps: int, n_layer: int, batch: int, block: int, n_hea
         torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
         losses.append(loss.item())
-    sd.uninstall()
+    (sd.install if was_patched else sd.uninstall)()  # leave the override as it was found
     return losses, torch.cuda.max_memory_allocated(), native.launch_count() - launches0
 
 

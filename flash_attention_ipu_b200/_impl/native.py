@@ -29,6 +29,7 @@ class Problem(Structure):  # fa_b200_problem
         ("B", c_int32), ("H", c_int32), ("Lq", c_int32), ("Lk", c_int32), ("D", c_int32),
         ("dtype", c_int32), ("causal", c_int32), ("softmax_scale", c_float),
         ("block_q_hint", c_int32), ("block_kv_hint", c_int32), ("q_pos0", c_int32), ("kv_pos0", c_int32),
+        ("H_kv", c_int32),
     ]
 
 
@@ -90,8 +91,11 @@ def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
     if q.dtype not in _DTYPES:
         raise RuntimeError(f"unsupported dtype {q.dtype}")
     B, H, Lq, D = q.shape
+    H_kv = k.shape[1]  # fewer K/V heads than query heads = grouped-query attention
+    if H % H_kv:
+        raise RuntimeError(f"{H} query heads are not a multiple of {H_kv} key/value heads")
     return Problem(B, H, Lq, k.shape[2], D, _DTYPES[q.dtype], int(bool(causal)), float(scale),
-                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0))
+                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv)
 
 
 def kernel_family(prob: Problem) -> int:

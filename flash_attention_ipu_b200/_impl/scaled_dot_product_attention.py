@@ -8,7 +8,8 @@ original function for tensors that are not on our device (:60-61).
 Changed (documented deviations): ``is_causal=False`` is routed to the
 kernel instead of raising (needed by BASELINE.json config 4); ``attn_mask is not None`` replaces
 the reference's ``if attn_mask:`` (which breaks on real tensors); torch >= 2.1's ``scale=`` and
-``enable_gqa=`` keywords are accepted; q is not pre-multiplied by D**-0.5 and stacked (:55-57) --
+``enable_gqa=`` keywords are accepted, and with ``enable_gqa=True`` grouped-query / multi-query
+shapes (fewer K/V heads, 16-bit, D in {64,128}) go to the kernels (the reference raises, :33-37); q is not pre-multiplied by D**-0.5 and stacked (:55-57) --
 the scale is folded into the kernel and q, k, v are consumed in place through their strides.
 """
 from math import ceil, floor, log2
@@ -42,7 +43,11 @@ def _sdpa_impl(
         raise NotImplementedError("flash_attention_ipu does not currently support passing attn_mask")
     if dropout_p > 0.0:
         raise NotImplementedError("flash_attention_ipu does not currently support non-zero dropout_p")
-    if query.shape != key.shape:
+    gqa = (enable_gqa and query.ndim == 4 and key.ndim == 4 and key.shape == value.shape
+           and query.shape[0] == key.shape[0] and query.shape[2:] == key.shape[2:]
+           and key.shape[1] > 0 and query.shape[1] % key.shape[1] == 0
+           and query.is_cuda and query.dtype in (torch.bfloat16, torch.float16) and query.shape[-1] in (64, 128))
+    if query.shape != key.shape and not enable_gqa:
         raise NotImplementedError(
             "flash_attention_ipu does not currently support Grouped- or Multi-query "
             "attention (query.shape != key.shape)"
@@ -52,9 +57,11 @@ def _sdpa_impl(
 
     on_device = (query.is_cuda and query.dtype in _SUPPORTED and query.ndim >= 2
                  and key.dtype == query.dtype and value.dtype == query.dtype
-                 and (query.shape[-1] <= 256))
+                 and (query.shape[-1] <= 256) and (query.shape == key.shape or gqa))
     if not on_device:
         kwargs = {} if scale is None else {"scale": scale}
+        if enable_gqa:
+            kwargs["enable_gqa"] = True
         return orig_fn(query, key, value, attn_mask, dropout_p, is_causal, **kwargs)
 
     L, D = query.shape[-2:]

@@ -41,6 +41,7 @@ int launched() {
 }
 
 size_t elem_size(int dtype) { return dtype == FA_B200_F32 ? 4 : 2; }
+int kv_heads(const fa_b200_problem *p) { return p->H_kv > 0 ? p->H_kv : p->H; }
 
 int check_problem(const fa_b200_problem *p) {
   if (!p) return fail(FA_B200_ERR_INVALID, "null problem");
@@ -50,6 +51,10 @@ int check_problem(const fa_b200_problem *p) {
   if (p->dtype < FA_B200_F16 || p->dtype > FA_B200_F32)
     return fail(FA_B200_ERR_UNSUPPORTED, "unknown dtype %d", p->dtype);
   if (!(p->softmax_scale > 0.f)) return fail(FA_B200_ERR_INVALID, "softmax_scale must be > 0");
+  if (p->H_kv < 0 || (p->H_kv > 0 && p->H % p->H_kv))
+    return fail(FA_B200_ERR_INVALID, "H_kv=%d must be 0 or a divisor of H=%d", p->H_kv, p->H);
+  if (p->H_kv > 0 && p->H_kv != p->H && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
+    return fail(FA_B200_ERR_UNSUPPORTED, "grouped-query attention needs the tensor path (16-bit, D in {64,128})");
   if (p->D > fa::kGenMaxD && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
     return fail(FA_B200_ERR_UNSUPPORTED, "head dim %d > %d", p->D, fa::kGenMaxD);
   return 0;
@@ -170,12 +175,13 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
                const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
   CUtensorMap tq, tk, tv, to;
   if (int rc = make_tmap(&tq, q, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
-  if (int rc = make_tmap(&tk, k, p->dtype, p->B, p->H, p->Lk, D, fa::kBlockN)) return rc;
-  if (int rc = make_tmap(&tv, v, p->dtype, p->B, p->H, p->Lk, D, fa::kBlockN)) return rc;
+  if (int rc = make_tmap(&tk, k, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
+  if (int rc = make_tmap(&tv, v, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
   if (int rc = make_tmap(&to, o, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
   fa::FwdParams fp;
   fp.lse = lse;
   fp.Lq = p->Lq; fp.Lk = p->Lk; fp.H = p->H;
+  fp.kv_ratio = p->H / kv_heads(p);
   fp.causal = p->causal;
   fp.shift = p->q_pos0 - p->kv_pos0;
   fp.scale_log2 = p->softmax_scale * fa::kLog2e;
@@ -239,15 +245,17 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
   CUtensorMap tq, tk, tv, tdo, tdq, tdk, tdv;
   if (int rc = make_tmap(&tq, q, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
-  if (int rc = make_tmap(&tk, k, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
-  if (int rc = make_tmap(&tv, v, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
+  const int Hkv = kv_heads(p);
+  if (int rc = make_tmap(&tk, k, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
+  if (int rc = make_tmap(&tv, v, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdo, dout, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
   if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32)) return rc;
-  if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
-  if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, p->H, p->Lk, D, 128)) return rc;
+  if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
+  if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
   bp.lse2 = lse2; bp.delta = delta;
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
+  bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;
   bp.causal = p->causal; bp.shift = p->q_pos0 - p->kv_pos0;
   bp.scale = p->softmax_scale; bp.scale_log2 = p->softmax_scale * fa::kLog2e;
   bp.num_kv_tiles = (p->Lk + 127) / 128;
@@ -258,7 +266,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
                                     fa::BwdSmem<D>::kBytes));
     attr_set = true;
   }
-  const unsigned grid = (unsigned)((int64_t)G * bp.num_kv_tiles);
+  const unsigned grid = (unsigned)((int64_t)p->B * Hkv * bp.num_kv_tiles);  // one CTA per (batch, K/V head, KV tile)
   kern<<<grid, fa::kBwdThreads, fa::BwdSmem<D>::kBytes, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, bp);
   if (int rc = launched()) return rc;
   // dQ = softmax_scale * dq_acc, cast to the output dtype

@@ -38,6 +38,7 @@ struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
   const float *delta;  // [G][Lq_pad]  -rowsum(O o dO); 0 for padding
   int Lq, Lk, H, Lq_pad;
+  int Hkv, kv_ratio;   // K/V heads and query heads per K/V head (H = Hkv * kv_ratio; 1 = multi-head)
   int causal, shift;
   float scale, scale_log2;
   int num_kv_tiles;    // ceil(Lk / 128)
@@ -94,12 +95,16 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
-  const int g = blockIdx.x / p.num_kv_tiles;
-  const int j = blockIdx.x % p.num_kv_tiles;  // ascending: the KV tiles with most Q tiles first
-  const int b = g / p.H, h = g % p.H;
+  const int gk = blockIdx.x / p.num_kv_tiles;  // (batch, K/V head)
+  const int j = blockIdx.x % p.num_kv_tiles;   // ascending: the KV tiles with most Q tiles first
+  const int b = gk / p.Hkv, hk = gk % p.Hkv;
   const int num_q_tiles = (p.Lq + 127) / 128;
   const int i0 = bwd_first_q_tile(p, j);
-  const int n = max(num_q_tiles - i0, 0);
+  // The CTA walks the Q tiles of every query head that shares this K/V head (grouped-query
+  // attention: kv_ratio heads; dK, dV simply keep accumulating in TMEM across them).
+  const int n1 = max(num_q_tiles - i0, 0);     // Q tiles per query head
+  const int n = n1 * p.kv_ratio;               // loop iterations; iteration it -> head it / n1, tile it % n1
+  const int h0 = hk * p.kv_ratio;
 
   if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) {
     printf("fa_b200: dynamic shared memory is not 1024-byte aligned\n");
@@ -129,13 +134,13 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (lane == 0 && n > 0) {
       mbar_arrive_expect_tx(kv_full, 2 * L::kTileBytes);
       for (int hh = 0; hh < kHalves; ++hh) {
-        tma_load_4d(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
-        tma_load_4d(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
+        tma_load_4d(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
+        tma_load_4d(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
       }
-      const float *lse_g = p.lse2 + static_cast<size_t>(g) * p.Lq_pad;
-      const float *delta_g = p.delta + static_cast<size_t>(g) * p.Lq_pad;
       for (int it = 0; it < n; ++it) {
-        const int i = i0 + it, s = it & 1;
+        const int h = h0 + it / n1, i = i0 + it % n1, s = it & 1;
+        const float *lse_g = p.lse2 + static_cast<size_t>(b * p.H + h) * p.Lq_pad;
+        const float *delta_g = p.delta + static_cast<size_t>(b * p.H + h) * p.Lq_pad;
         mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
 #ifdef FA_EXPERIMENT_HALF_LOADS  // timing experiment only (wrong results): skip every other tile load
         if ((it & 3) >= 2) {
@@ -257,7 +262,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
     uint8_t *wstage = smem + L::kDQOff + w * 8192;
     for (int it = 0; it < n; ++it) {
-      const int i = i0 + it;
+      const int h = h0 + it / n1, i = i0 + it % n1;
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
       #pragma unroll
@@ -305,7 +310,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int key = j * 128 + row;
 
     for (int it = 0; it < n; ++it) {
-      const int i = i0 + it;
+      const int i = i0 + it % n1;
       const float4 *stat = reinterpret_cast<const float4 *>(smem + L::kStatOff + (it & 1) * 1024) + wg * 16;
       mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
       // -lse2 of this warpgroup's 64 query columns: loaded (broadcast LDS.128) BEFORE the S^T wait so
@@ -441,8 +446,8 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     named_bar_sync(2, 256);
     if (threadIdx.x == 0) {
       for (int hh = 0; hh < kHalves; ++hh) {
-        tma_store_4d(&tmDK, smem + L::kQOff + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
-        tma_store_4d(&tmDV, smem + L::kQOff + L::kTileBytes + hh * L::kHalfBytes, hh * 64, j * 128, h, b);
+        tma_store_4d(&tmDK, smem + L::kQOff + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
+        tma_store_4d(&tmDV, smem + L::kQOff + L::kTileBytes + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
       }
       tma_store_commit();
       tma_store_wait<0>();

@@ -55,6 +55,7 @@ constexpr float kRescaleThreshold = 8.0f;  // lazy O rescale: only when the max 
 struct FwdParams {
   float *lse;         // [G][Lq] fp32
   int Lq, Lk, H;      // H: heads per batch (group g -> (b = g / H, h = g % H))
+  int kv_ratio;       // query heads per K/V head (1 = multi-head; >1 = grouped-query attention)
   int causal;
   int shift;          // q_pos0 - kv_pos0: key c visible to query r iff c <= r + shift
   float scale_log2;   // softmax_scale * log2(e)
@@ -171,12 +172,12 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_arrive_expect_tx(&k_full[ks], L::kTileBytes);
         for (int hh = 0; hh < kHalves; ++hh)
           tma_load_4d(&tmK, &k_full[ks], smem + L::kKOff + ks * L::kTileBytes + hh * L::kHalfBytes,
-                      hh * 64, j * kBlockN, h, b);
+                      hh * 64, j * kBlockN, h / p.kv_ratio, b);
         mbar_wait(&v_empty[vs], ((j / kVStages) & 1) ^ 1);
         mbar_arrive_expect_tx(&v_full[vs], L::kTileBytes);
         for (int hh = 0; hh < kHalves; ++hh)
           tma_load_4d(&tmV, &v_full[vs], smem + L::kVOff + vs * L::kTileBytes + hh * L::kHalfBytes,
-                      hh * 64, j * kBlockN, h, b);
+                      hh * 64, j * kBlockN, h / p.kv_ratio, b);
       }
     }
   } else if (warp == 9) {

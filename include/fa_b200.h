@@ -56,6 +56,10 @@ typedef struct {
   int32_t block_q_hint;  /* L/num_chunks_q  of the reference API: a tile-size HINT only   */
   int32_t block_kv_hint; /* L/num_chunks_kv (cpp/flash_attention_qkv_packed.cpp:194-195)  */
   int32_t q_pos0, kv_pos0; /* global sequence position of q row 0 / kv row 0 (ring steps) */
+  int32_t H_kv;          /* K/V heads: 0 or H = multi-head; a divisor of H = grouped-query /  */
+                         /* multi-query attention (query head h reads K/V head h/(H/H_kv));   */
+                         /* k, v, dk, dv are then (B, H_kv, Lk, D).  The reference refuses    */
+                         /* this case (_impl/scaled_dot_product_attention.py:33-37).          */
 } fa_b200_problem;
 
 /* Forward: replaces flashAttentionQKVPackedWithStash

@@ -328,3 +328,35 @@ def test_host_streamed_attention_matches_device_path():
     # dQ accumulates by fp32 atomics in a different order per launch: equal up to that
     assert (h_dqkv.float() - x.grad.float().cpu()).abs().max().item() <= 2e-2
     assert torch.equal(h_dqkv[1:], x.grad[1:].cpu())
+
+
+@pytest.mark.parametrize("Hq,Hkv,L,D", [(8, 2, 512, 128), (6, 1, 384, 64), (4, 4, 256, 128)])
+@pytest.mark.parametrize("causal", [True, False])
+def test_grouped_query_attention(Hq, Hkv, L, D, causal):
+    """Grouped-/multi-query attention (fewer K/V heads) through the SDPA override with
+    enable_gqa=True -- an extension: the reference raises for q.shape != k.shape
+    (_impl/scaled_dot_product_attention.py:33-37).  Oracle: the same math with K/V heads repeated."""
+    native = _native_loaded()
+    from flash_attention_ipu_b200._impl import scaled_dot_product_attention as sd
+    sd.install()
+    launches0 = native.launch_count()
+    torch.manual_seed(SEED)
+    B = 2
+    q = torch.randn(B, Hq, L, D).bfloat16()
+    k, v = torch.randn(B, Hkv, L, D).bfloat16(), torch.randn(B, Hkv, L, D).bfloat16()
+    dout = torch.randn(B, Hq, L, D).bfloat16()
+    qd, kd, vd = (t.cuda().requires_grad_(True) for t in (q, k, v))
+    out = torch.nn.functional.scaled_dot_product_attention(qd, kd, vd, is_causal=causal, enable_gqa=True)
+    out.backward(dout.cuda())
+    torch.cuda.synchronize()
+    assert native.launch_count() - launches0 >= 2, "the override did not route to the CUDA kernels"
+    qf, kf, vf = (t.float().requires_grad_(True) for t in (q, k, v))
+    rep = Hq // Hkv
+    ref = ao.sdpa_reference(qf, kf.repeat_interleave(rep, dim=1), vf.repeat_interleave(rep, dim=1), is_causal=causal)
+    ref.backward(dout.float())
+    assert (out.float().cpu() - ref.detach()).abs().max().item() <= 1e-2
+    for got, want in ((qd.grad, qf.grad), (kd.grad, kf.grad), (vd.grad, vf.grad)):
+        assert got.shape == want.shape
+        assert rel_fro(got.float().cpu(), want) <= 1e-2
+    with pytest.raises(NotImplementedError):  # without the flag the reference behaviour is kept
+        torch.nn.functional.scaled_dot_product_attention(qd, kd[:, :1], vd[:, :1], is_causal=causal)
