@@ -9,7 +9,7 @@ NVFLAGS ?= -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-Wall -Xptxas -v
 CSRC    := flash_attention_ipu_b200/csrc
 HDRS    := $(wildcard $(CSRC)/*.cuh) include/fa_b200.h
 
-all: $(OUT)/libflash_attention.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe
+all: $(OUT)/libflash_attention.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe $(OUT)/umma_rate $(OUT)/exp_rate
 
 $(OUT)/libflash_attention.so: $(CSRC)/fa_api.cu $(HDRS)
 	@mkdir -p $(OUT)
@@ -29,6 +29,15 @@ $(OUT)/tests: tests/cuda/test_flash_attention.cu oracle/vanilla_attention.c $(OU
 $(OUT)/umma_probe: tests/cuda/umma_probe.cu $(CSRC)/sm100_ptx.cuh
 	@mkdir -p $(OUT)
 	$(NVCC) -std=c++17 -O2 -lineinfo $(ARCH) -o $@ $<
+
+# microbenchmarks behind DESIGN.md section 4.5 (tensor-pipe issue rate, exponential throughput)
+$(OUT)/umma_rate: tests/cuda/umma_rate.cu $(CSRC)/sm100_ptx.cuh
+	@mkdir -p $(OUT)
+	$(NVCC) -std=c++17 -O2 -lineinfo $(ARCH) -o $@ $<
+
+$(OUT)/exp_rate: tests/cuda/exp_rate.cu $(CSRC)/sm100_ptx.cuh
+	@mkdir -p $(OUT)
+	$(NVCC) -std=c++17 -O3 -lineinfo $(ARCH) -o $@ $<
 
 clean:
 	rm -rf $(OUT)

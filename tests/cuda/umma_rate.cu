@@ -50,6 +50,46 @@ __global__ void __launch_bounds__(384, 1) rate_kernel(int iters, long long *out,
                    i_mnmn = make_idesc(128, 128, 1, 1, 1), i_kk256 = make_idesc(128, 256, 1, 0, 0),
                    i_kk64 = make_idesc(128, 64, 1, 0, 0);
     const long long t0 = clock64();
+    if (mode >= 23) {
+      // straight-line rotation (no per-MMA branching): per iteration S0, PV1, S1, PV0, 8 MMAs each.
+      // 23: as the forward kernel.  24: PV reads A from the other tile's columns (no WAR on the
+      // S accumulator that the next GEMM overwrites).  25: all four GEMMs SS.  26: all four TS.
+      for (int it = 0; it < iters / 4; ++it) {
+        mbar_wait_lean(&bar2[3], 1); tc_fence_after();
+        if (leader) {
+          const uint32_t a0 = (mode == 24) ? tm + 128 : tm, a1 = (mode == 24) ? tm : tm + 128;
+          #pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t offk = ((k / 4) * 16384 + (k % 4) * 32) >> 4;
+            if (mode == 26) umma_ts2(tm, tm + 256 + k * 8, b_k + offk, hi, i_kk, k > 0);
+            else umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, k > 0);
+          }
+          umma_commit(&bar2[0]);
+          #pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t offk = ((k / 4) * 16384 + (k % 4) * 32) >> 4, offmn = k * (2048 >> 4);
+            if (mode == 25) umma_ss2(tm + 384, a_k + offk, hi, b_mn + offmn, hi, i_kmn, 1);
+            else umma_ts2(tm + 384, a1 + k * 8, b_mn + offmn, hi, i_kmn, 1);
+          }
+          umma_commit(&bar2[0]);
+          #pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t offk = ((k / 4) * 16384 + (k % 4) * 32) >> 4;
+            if (mode == 26) umma_ts2(tm + 128, tm + 320 + k * 8, b_k + offk, hi, i_kk, k > 0);
+            else umma_ss2(tm + 128, a_k + offk, hi, b_k + offk, hi, i_kk, k > 0);
+          }
+          umma_commit(&bar2[0]);
+          #pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint32_t offk = ((k / 4) * 16384 + (k % 4) * 32) >> 4, offmn = k * (2048 >> 4);
+            if (mode == 25) umma_ss2(tm + 256, a_k + offk, hi, b_mn + offmn, hi, i_kmn, 1);
+            else umma_ts2(tm + 256, a0 + k * 8, b_mn + offmn, hi, i_kmn, 1);
+          }
+          umma_commit(&bar2[0]);
+        }
+        __syncwarp();
+      }
+    } else
     for (int it = 0; it < iters; ++it) {
       if (mode == 11 || mode == 12) tc_fence_after();
       if (mode == 12) { mbar_wait(&bar2[3], 1); }       // a wait that is already satisfied (bounded-spin form)
@@ -71,7 +111,16 @@ __global__ void __launch_bounds__(384, 1) rate_kernel(int iters, long long *out,
           case 5: umma_ss2(tm, a_k + offk, hi, b_mn + offmn, hi, i_kmn, 1); break;           // dK = dS^T Q
           case 6: umma_ts2(tm + 256, tm + k * 8, b_k + offk, hi, i_kk, 1); break;            // TS, B K-major
           case 8: case 10: umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, 1); break;     // + commits
-          case 9: case 7: case 11: case 12: case 13: case 17: case 18: case 19: if (it & 1) umma_ts2(tm + 256, tm + k * 8, b_mn + offmn, hi, i_kmn, 1);    // fwd mix
+          case 9: case 7: case 11: case 12: case 13: case 20: case 21: case 22: {  // the forward's exact accumulator rotation: S0 PV1 S1 PV0
+            const int ph = it & 3;
+            const uint32_t acc = (mode == 21) ? 1u : (k > 0);   // 21: never start a fresh accumulator
+            if (mode == 22 && (ph & 1) == 0) { umma_ss2(tm + 64 * ph, a_k + offk, hi, b_k + offk, hi, i_kk, 1); break; }  // 22: S only, acc=1
+            if (ph == 0) umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, acc);
+            else if (ph == 1) umma_ts2(tm + 384, tm + 128 + k * 8, b_mn + offmn, hi, i_kmn, 1);
+            else if (ph == 2) umma_ss2(tm + 128, a_k + offk + (32768 >> 4), hi, b_k + offk, hi, i_kk, acc);
+            else umma_ts2(tm + 256, tm + k * 8, b_mn + offmn, hi, i_kmn, 1);
+            break; }
+          case 17: case 18: case 19: if (it & 1) umma_ts2(tm + 256, tm + k * 8, b_mn + offmn, hi, i_kmn, 1);    // fwd mix
                   else umma_ss2(tm, a_k + offk, hi, b_k + offk, hi, i_kk, 1); break;
         }
         if (mode == 10 && k == 3) umma_commit(&bar2[1]);
@@ -102,18 +151,22 @@ int main() {
                          "NO MMAs: one satisfied mbarrier wait per iteration (clk per 8 = per wait / 8)",
                          "NO MMAs: satisfied wait + tcgen05.fence::after per iteration", "NO MMAs: 4 satisfied waits per iteration",
                          "warp loop, forward mix, B descriptor changes every GEMM (ring stage) + commit", "mode 17 + satisfied wait + fence per GEMM",
-                         "mode 18 + 11 bystander warps spinning on mbarrier.try_wait"};
-  const int nominal[] = {64, 64, 64, 128, 32, 64, 64, 64, 64, 64, 64, 64, 64, 64, 0, 0, 0, 64, 64, 64};
+                         "mode 18 + 11 bystander warps spinning on mbarrier.try_wait",
+                         "forward accumulator rotation S0 PV1 S1 PV0 (4 TMEM accumulators) + wait/fence/commit",
+                         "mode 20 with accumulate=1 on every MMA (no fresh accumulator)", "mode 21 (same, control)",
+                         "straight-line S0 PV1 S1 PV0 exactly as the forward kernel", "as 23 but PV reads P from the OTHER tile's S columns",
+                         "as 23 with all four GEMMs SS", "as 23 with all four GEMMs TS"};
+  const int nominal[] = {64, 64, 64, 128, 32, 64, 64, 64, 64, 64, 64, 64, 64, 64, 0, 0, 0, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64};
   long long *d, h[148];
   cudaMalloc(&d, sizeof(h));
   const int iters = 512;
-  void (*kerns[20])(int, long long *, int) = {rate_kernel<0>, rate_kernel<1>, rate_kernel<2>, rate_kernel<3>,
+  void (*kerns[27])(int, long long *, int) = {rate_kernel<0>, rate_kernel<1>, rate_kernel<2>, rate_kernel<3>,
                                         rate_kernel<4>, rate_kernel<5>, rate_kernel<6>, rate_kernel<7>,
                                         rate_kernel<8>, rate_kernel<9>, rate_kernel<10>,
                                         rate_kernel<11>, rate_kernel<12>, rate_kernel<13>,
-                                        rate_kernel<14>, rate_kernel<15>, rate_kernel<16>, rate_kernel<17>, rate_kernel<18>, rate_kernel<19>};
+                                        rate_kernel<14>, rate_kernel<15>, rate_kernel<16>, rate_kernel<17>, rate_kernel<18>, rate_kernel<19>, rate_kernel<20>, rate_kernel<21>, rate_kernel<22>, rate_kernel<23>, rate_kernel<24>, rate_kernel<25>, rate_kernel<26>};
   for (int rnd = 0; rnd < 2; ++rnd)
-  for (int mode = 0; mode < 20; ++mode) {
+  for (int mode = 0; mode < 27; ++mode) {
     if (rnd && mode != 0 && mode != 1 && mode != 7) continue;
     if (rnd) printf("random operand data: ");
     cudaFuncSetAttribute(kerns[mode], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
