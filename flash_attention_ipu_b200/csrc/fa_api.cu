@@ -12,6 +12,7 @@
 #include "fa_bwd_sm100.cuh"
 #include "fa_fwd_sm100.cuh"
 #include "fa_generic.cuh"
+#include "fa_tiled_simt.cuh"
 
 namespace {
 
@@ -132,9 +133,31 @@ fa::GenericParams gparams(const fa_b200_problem *p) {
 unsigned blocks_for(int64_t rows, int per_block) { return (unsigned)((rows + per_block - 1) / per_block); }
 
 // ---------------------------------------------------------------- generic family
+// D <= 128: shared-memory tiled FFMA kernels (fa_tiled_simt.cuh); 128 < D <= 256: warp-per-row.
+unsigned tiles(int rows) { return (unsigned)((rows + fa::kTB - 1) / fa::kTB); }
+
+template <typename K>
+int allow_smem(K kernel, size_t bytes) {
+  FA_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+template <typename T, int DP>
+int tiled_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+              const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  auto kern = fa::fa_tiled_fwd_kernel<T, DP>;
+  static int once = allow_smem(kern, fa::t_fwd_smem<DP>());
+  if (once) return once;
+  kern<<<dim3(tiles(p->Lq), (unsigned)(p->B * p->H)), fa::kTThreads, fa::t_fwd_smem<DP>(), st>>>(
+      view<const T>(q), view<const T>(k), view<const T>(v), view<T>(o), lse, gparams(p));
+  return launched();
+}
+
 template <typename T>
 int generic_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
                 const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  if (p->D <= 64) return tiled_fwd<T, 64>(p, q, k, v, o, lse, st);
+  if (p->D <= 128) return tiled_fwd<T, 128>(p, q, k, v, o, lse, st);
   const int64_t rows = (int64_t)p->B * p->H * p->Lq;
   fa::fa_generic_fwd_kernel<T><<<blocks_for(rows, fa::kGenWarps), fa::kGenWarps * 32,
                                  fa::kGenWarps * p->D * sizeof(float), st>>>(
@@ -151,12 +174,34 @@ int launch_delta(const fa_b200_problem *p, const fa_b200_tensor *o, const fa_b20
   return launched();
 }
 
+template <typename T, int DP>
+int tiled_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+              const fa_b200_tensor *v, const fa_b200_tensor *dout, const float *lse,
+              const fa_b200_tensor *dq, const fa_b200_tensor *dk, const fa_b200_tensor *dv,
+              const float *delta, cudaStream_t st) {
+  auto kq = fa::fa_tiled_bwd_dq_kernel<T, DP>;
+  auto kkv = fa::fa_tiled_bwd_dkv_kernel<T, DP>;
+  static int once = [&] { int rc = allow_smem(kq, fa::t_bwd_smem<DP>()); return rc ? rc : allow_smem(kkv, fa::t_bwd_smem<DP>()); }();
+  if (once) return once;
+  const unsigned groups = (unsigned)(p->B * p->H);
+  kq<<<dim3(tiles(p->Lq), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
+      view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
+      view<T>(dq), gparams(p));
+  if (int rc = launched()) return rc;
+  kkv<<<dim3(tiles(p->Lk), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
+      view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
+      view<T>(dk), view<T>(dv), gparams(p));
+  return launched();
+}
+
 template <typename T>
 int generic_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
                 const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
                 const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
                 const fa_b200_tensor *dv, float *delta, cudaStream_t st) {
   if (int rc = launch_delta<T>(p, o, dout, delta, st)) return rc;
+  if (p->D <= 64) return tiled_bwd<T, 64>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
+  if (p->D <= 128) return tiled_bwd<T, 128>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
   const int64_t qrows = (int64_t)p->B * p->H * p->Lq, krows = (int64_t)p->B * p->H * p->Lk;
   const size_t sm = fa::kGenWarps * 2 * p->D * sizeof(float);
   fa::fa_generic_bwd_dq_kernel<T><<<blocks_for(qrows, fa::kGenWarps), fa::kGenWarps * 32, sm, st>>>(

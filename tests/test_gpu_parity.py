@@ -360,3 +360,56 @@ def test_grouped_query_attention(Hq, Hkv, L, D, causal):
         assert rel_fro(got.float().cpu(), want) <= 1e-2
     with pytest.raises(NotImplementedError):  # without the flag the reference behaviour is kept
         torch.nn.functional.scaled_dot_product_attention(qd, kd[:, :1], vd[:, :1], is_causal=causal)
+
+
+def _blocked_reference(q, k, v, dout, causal, shift, scale):
+    """fp64 attention of one (query block, key block) pair: key c visible to query r iff
+    c <= r + shift; a row that sees nothing gives out = 0, lse = -inf and no gradient."""
+    q, k, v = (t.double().requires_grad_(True) for t in (q, k, v))
+    s = torch.einsum("bhqd,bhkd->bhqk", q, k) * scale
+    if causal:
+        r = torch.arange(q.shape[2])[:, None]
+        c = torch.arange(k.shape[2])[None, :]
+        s = s.masked_fill(c > r + shift, float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)
+    p = torch.where(torch.isinf(lse)[..., None], torch.zeros_like(s), torch.exp(s - lse[..., None].clamp_min(-1e300)))
+    out = torch.einsum("bhqk,bhkd->bhqd", p, v)
+    out.backward(dout.double())
+    return out.detach(), lse.detach(), q.grad, k.grad, v.grad
+
+
+@pytest.mark.parametrize("B,H,Lq,Lk,D,causal,q0,k0,dtype", [
+    (2, 3, 200, 200, 128, True, 0, 0, "fp32"),
+    (1, 2, 331, 331, 64, True, 0, 0, "fp32"),
+    (1, 2, 70, 150, 40, False, 0, 0, "fp32"),
+    (1, 2, 100, 130, 96, True, 64, 0, "fp32"),     # query block later than the key block
+    (1, 1, 90, 130, 24, True, 0, 40, "fp32"),      # first 40 rows see no key at all
+    (1, 1, 1, 1, 8, True, 0, 0, "fp32"),
+    (2, 2, 65, 65, 72, True, 0, 0, "bf16"),        # 16-bit input, head dim off the tensor path
+    (1, 2, 129, 257, 100, False, 0, 0, "fp16"),
+])
+def test_tiled_simt_kernels(B, H, Lq, Lk, D, causal, q0, k0, dtype):
+    """csrc/fa_tiled_simt.cuh through the C ABI: ragged lengths, padded head dims, shifted causal
+    diagonals (the ring's block positions) and rows with nothing visible, against fp64 math."""
+    native = _native_loaded()
+    torch.manual_seed(SEED + Lq + D)
+    dt = DT[dtype]
+    q, k, v, dout = (torch.randn(B, H, L, D).to(dt) for L in (Lq, Lk, Lk, Lq))
+    scale = D ** -0.5
+    ref = _blocked_reference(q.float(), k.float(), v.float(), dout.float(), causal, q0 - k0, scale)
+    qd, kd, vd, dd = (t.cuda() for t in (q, k, v, dout))
+    prob = native.make_problem(qd, kd, causal, scale, 0, 0, q0, k0)
+    assert native.kernel_family(prob) == 0
+    o = torch.empty_like(qd)
+    lse = torch.empty(B, H, Lq, device="cuda", dtype=torch.float32)
+    native.fwd(prob, qd, kd, vd, o, lse)
+    dq, dk, dv = torch.empty_like(qd), torch.empty_like(kd), torch.empty_like(vd)
+    ws = torch.empty(max(native.bwd_workspace_bytes(prob), 4), device="cuda", dtype=torch.uint8)
+    native.bwd(prob, qd, kd, vd, o, dd, lse, dq, dk, dv, ws)
+    torch.cuda.synchronize()
+    atol = 2e-4 if dtype == "fp32" else 3e-2
+    assert torch.equal(torch.isinf(lse.cpu()), torch.isinf(ref[1]))
+    fin = ~torch.isinf(ref[1])
+    assert (lse.cpu().double()[fin] - ref[1][fin]).abs().max().item() <= (1e-4 if dtype == "fp32" else 1e-2)
+    for got, want in zip((o, dq, dk, dv), (ref[0], ref[2], ref[3], ref[4])):
+        assert (got.cpu().double() - want).abs().max().item() <= atol
