@@ -437,7 +437,7 @@ def run_small(args):
         "config": {"workload": w["name"], "api": "F.scaled_dot_product_attention (flash_attention_ipu.auto)",
                    "l2": "256 MB flush buffer written between timed iterations",
                    "launch": "fwd+bwd captured in one CUDA graph and replayed (eager time in chunk_sweep)",
-                   "kernel_family": "generic SIMT (fp32 inputs)" if w["dtype"] == "fp32" else "tcgen05"},
+                   "kernel_family": "tiled SIMT fp32 (FFMA2, csrc/fa_tiled_simt.cuh)" if w["dtype"] == "fp32" else "tcgen05"},
         "gpu_launches": int(r0["launches_per_step"] * args.steps), "chunk_sweep": results}), flush=True)
 
 

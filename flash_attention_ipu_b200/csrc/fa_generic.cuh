@@ -304,18 +304,23 @@ fa_merge_acc_kernel(float *o_acc, float *lse_acc, const T *o_b, const float *lse
 template <typename T>
 __global__ void __launch_bounds__(256)
 fa_convert_kernel(const float *src, View<T> dst, int B, int H, int L, int D, float scale) {
-  const int64_t n4 = static_cast<int64_t>(B) * H * L * D / 4;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+  static_assert(sizeof(T) == 2, "16-bit outputs only (8 elements = one 16-byte store)");
+  const int64_t n8 = static_cast<int64_t>(B) * H * L * D / 8;  // D is 64 or 128 on this path
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const float4 x = reinterpret_cast<const float4 *>(src)[i];
-    const int64_t e = i * 4;
+    const float4 x = __ldcs(reinterpret_cast<const float4 *>(src) + 2 * i);
+    const float4 y = __ldcs(reinterpret_cast<const float4 *>(src) + 2 * i + 1);
+    const int64_t e = i * 8;
     const int d = static_cast<int>(e % D);
     const int64_t rowid = e / D;
     const int l = static_cast<int>(rowid % L);
     const int g = static_cast<int>(rowid / L);
-    T *out = dst.row(g / H, g % H, l) + d;
+    alignas(16) T out[8];
     out[0] = from_f32<T>(x.x * scale); out[1] = from_f32<T>(x.y * scale);
     out[2] = from_f32<T>(x.z * scale); out[3] = from_f32<T>(x.w * scale);
+    out[4] = from_f32<T>(y.x * scale); out[5] = from_f32<T>(y.y * scale);
+    out[6] = from_f32<T>(y.z * scale); out[7] = from_f32<T>(y.w * scale);
+    *reinterpret_cast<uint4 *>(dst.row(g / H, g % H, l) + d) = *reinterpret_cast<const uint4 *>(out);
   }
 }
 

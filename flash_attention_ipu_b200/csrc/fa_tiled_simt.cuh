@@ -17,9 +17,15 @@
 //   * head dims below the padded width DP (64 or 128) are zero-filled in shared memory.
 //   * backward = two kernels (dQ with Q stationary, dK/dV with K/V stationary and the score tile
 //     transposed), no atomics: results are deterministic.
+//   * the inner products are issued as packed fma.rn.f32x2 (SASS FFMA2): a 3-register FFMA
+//     issues every other cycle per SM sub-partition, FFMA2 does two FMAs in the same slot, so it
+//     is the only way to the fp32 peak.  NT packs along the contraction (even/odd partial sums,
+//     the float4 operand loads are already register pairs); NN packs along the output columns
+//     with the P value duplicated into both halves.
 // Exponentials are exp2 with log2(e) folded into the stationary operand's scale.
 #pragma once
 #include "fa_generic.cuh"
+#include "sm100_ptx.cuh"
 
 namespace fa {
 
@@ -61,33 +67,71 @@ __device__ __forceinline__ void t_load_tile(float *dst, const T *slab, int64_t s
   }
 }
 
-template <int DP>
+// c[i][j] += sum_d A[ty + 8 i][d] * B[tx + 16 j][d].  kPacked: FFMA2 over (even d, odd d) partial
+// sums (64 transient accumulator registers); otherwise scalar FFMA (32), for the register-bound
+// dK/dV kernel at DP = 128.
+template <int DP, bool kPacked>
 __device__ __forceinline__ void t_gemm_nt(const float *A, const float *B, int ty, int tx, float (&c)[8][4]) {
   constexpr int LD = DP + 4;
-  #pragma unroll 2
-  for (int d = 0; d < DP; d += 4) {
-    float4 a[8], b[4];
+  if constexpr (kPacked) {
+    uint64_t c2[8][4];
     #pragma unroll
-    for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const float4 *>(A + (ty + 8 * i) * LD + d);
-    #pragma unroll
-    for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4 *>(B + (tx + 16 * j) * LD + d);
+    for (int i = 0; i < 8; ++i) {
+      #pragma unroll
+      for (int j = 0; j < 4; ++j) c2[i][j] = 0ull;
+    }
+    #pragma unroll 2
+    for (int d = 0; d < DP; d += 4) {
+      ulonglong2 a[8], b[4];
+      #pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const ulonglong2 *>(A + (ty + 8 * i) * LD + d);
+      #pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const ulonglong2 *>(B + (tx + 16 * j) * LD + d);
+      #pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          c2[i][j] = f2_fma(a[i].x, b[j].x, c2[i][j]);
+          c2[i][j] = f2_fma(a[i].y, b[j].y, c2[i][j]);
+        }
+      }
+    }
     #pragma unroll
     for (int i = 0; i < 8; ++i) {
       #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        c[i][j] = fmaf(a[i].x, b[j].x, c[i][j]);
-        c[i][j] = fmaf(a[i].y, b[j].y, c[i][j]);
-        c[i][j] = fmaf(a[i].z, b[j].z, c[i][j]);
-        c[i][j] = fmaf(a[i].w, b[j].w, c[i][j]);
+        float lo, hi;
+        f2_unpack(c2[i][j], lo, hi);
+        c[i][j] += lo + hi;
+      }
+    }
+  } else {
+    #pragma unroll 2
+    for (int d = 0; d < DP; d += 4) {
+      float4 a[8], b[4];
+      #pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const float4 *>(A + (ty + 8 * i) * LD + d);
+      #pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4 *>(B + (tx + 16 * j) * LD + d);
+      #pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          c[i][j] = fmaf(a[i].x, b[j].x, c[i][j]);
+          c[i][j] = fmaf(a[i].y, b[j].y, c[i][j]);
+          c[i][j] = fmaf(a[i].z, b[j].z, c[i][j]);
+          c[i][j] = fmaf(a[i].w, b[j].w, c[i][j]);
+        }
       }
     }
   }
 }
 
-// o[i][:] += sum_c P[ty + 8 i][c] * Y[c][:]; the thread owns columns tx*4 .. tx*4+3 (+64 for DP=128)
+// o[i][:] += sum_c P[ty + 8 i][c] * Y[c][:]; the thread owns columns tx*4 .. tx*4+3 (+64 for
+// DP=128), held as packed pairs: o[i][2 jj] = columns (0,1), o[i][2 jj + 1] = columns (2,3).
 template <int DP>
 __device__ __forceinline__ void t_gemm_nn(const float *P, const float *Y, int ty, int tx,
-                                          float (&o)[8][DP / 16]) {
+                                          uint64_t (&o)[8][DP / 32]) {
   constexpr int LD = DP + 4, NJ = DP / 64;
   #pragma unroll 1
   for (int c = 0; c < kTB; c += 4) {
@@ -96,19 +140,18 @@ __device__ __forceinline__ void t_gemm_nn(const float *P, const float *Y, int ty
     for (int i = 0; i < 8; ++i) pr[i] = *reinterpret_cast<const float4 *>(P + (ty + 8 * i) * kTLdp + c);
     #pragma unroll
     for (int cc = 0; cc < 4; ++cc) {
-      float4 y[NJ];
+      ulonglong2 y[NJ];
       #pragma unroll
       for (int jj = 0; jj < NJ; ++jj)
-        y[jj] = *reinterpret_cast<const float4 *>(Y + (c + cc) * LD + tx * 4 + 64 * jj);
+        y[jj] = *reinterpret_cast<const ulonglong2 *>(Y + (c + cc) * LD + tx * 4 + 64 * jj);
       #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float pv = cc == 0 ? pr[i].x : cc == 1 ? pr[i].y : cc == 2 ? pr[i].z : pr[i].w;
+        const uint64_t pp = f2_pack(pv, pv);
         #pragma unroll
         for (int jj = 0; jj < NJ; ++jj) {
-          o[i][jj * 4 + 0] = fmaf(pv, y[jj].x, o[i][jj * 4 + 0]);
-          o[i][jj * 4 + 1] = fmaf(pv, y[jj].y, o[i][jj * 4 + 1]);
-          o[i][jj * 4 + 2] = fmaf(pv, y[jj].z, o[i][jj * 4 + 2]);
-          o[i][jj * 4 + 3] = fmaf(pv, y[jj].w, o[i][jj * 4 + 3]);
+          o[i][jj * 2 + 0] = f2_fma(pp, y[jj].x, o[i][jj * 2 + 0]);
+          o[i][jj * 2 + 1] = f2_fma(pp, y[jj].y, o[i][jj * 2 + 1]);
         }
       }
     }
@@ -117,18 +160,20 @@ __device__ __forceinline__ void t_gemm_nn(const float *P, const float *Y, int ty
 
 template <int DP, typename T>
 __device__ __forceinline__ void t_store_rows(T *slab, int64_t sl, int row0, int nrows, int D, int ty, int tx,
-                                             const float (&acc)[8][DP / 16], const float (&mul)[8]) {
+                                             const uint64_t (&acc)[8][DP / 32], const float (&mul)[8]) {
   #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int r = row0 + ty + 8 * i;
     if (r >= nrows) continue;
     T *row = slab + r * sl;
     #pragma unroll
-    for (int jj = 0; jj < DP / 64; ++jj) {
+    for (int e2 = 0; e2 < DP / 32; ++e2) {
+      float x[2];
+      f2_unpack(acc[i][e2], x[0], x[1]);
       #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int d = tx * 4 + 64 * jj + e;
-        if (d < D) row[d] = from_f32<T>(acc[i][jj * 4 + e] * mul[i]);
+      for (int e = 0; e < 2; ++e) {
+        const int d = tx * 4 + 64 * (e2 / 2) + 2 * (e2 % 2) + e;
+        if (d < D) row[d] = from_f32<T>(x[e] * mul[i]);
       }
     }
   }
@@ -144,7 +189,7 @@ __global__ void __launch_bounds__(kTThreads)
 fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o, float *lse,
                     GenericParams p) {
   extern __shared__ __align__(16) float tsm[];
-  constexpr int LD = DP + 4, NC = DP / 16;
+  constexpr int LD = DP + 4, NC = DP / 32;
   float *Qs = tsm, *Ks = Qs + kTB * LD, *Vs = Ks + kTB * LD, *Ps = Vs + kTB * LD;
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   const int g = blockIdx.y, b = g / p.H, h = g % p.H;
@@ -153,12 +198,13 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
   int hi = p.Lk;
   if (p.causal) hi = min(hi, m0 + kTB + p.shift);  // last row of the tile sees keys < m0+63+shift+1
 
-  float acc[8][NC], m[8], l[8];
+  uint64_t acc[8][NC];
+  float m[8], l[8];
   #pragma unroll
   for (int i = 0; i < 8; ++i) {
     m[i] = -INFINITY; l[i] = 0.f;
     #pragma unroll
-    for (int c = 0; c < NC; ++c) acc[i][c] = 0.f;
+    for (int c = 0; c < NC; ++c) acc[i][c] = 0ull;
   }
   const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
   for (int n0 = 0; n0 < hi; n0 += kTB) {
@@ -169,7 +215,7 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
     float s[8][4];
     #pragma unroll
     for (int i = 0; i < 8; ++i) { s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f; }
-    t_gemm_nt<DP>(Qs, Ks, ty, tx, s);
+    t_gemm_nt<DP, true>(Qs, Ks, ty, tx, s);
     const bool edge = (n0 + kTB > p.Lk) || (p.causal && n0 + kTB - 1 > m0 + p.shift);
     if (edge) {
       #pragma unroll
@@ -197,8 +243,9 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
       }
       l[i] = l[i] * corr + part;  // per-thread partial sum; reduced over the 16 lanes at the end
       m[i] = m_new;
+      const uint64_t cc2 = f2_pack(corr, corr);
       #pragma unroll
-      for (int c = 0; c < NC; ++c) acc[i][c] *= corr;
+      for (int c = 0; c < NC; ++c) acc[i][c] = f2_mul(acc[i][c], cc2);
     }
     __syncwarp();
     t_gemm_nn<DP>(Ps, Vs, ty, tx, acc);
@@ -223,7 +270,7 @@ __global__ void __launch_bounds__(kTThreads)
 fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<const T> dout,
                        const float *lse, const float *delta, View<T> dq, GenericParams p) {
   extern __shared__ __align__(16) float tsm[];
-  constexpr int LD = DP + 4, NC = DP / 16;
+  constexpr int LD = DP + 4, NC = DP / 32;
   float *Qs = tsm, *Ds = Qs + kTB * LD, *Ks = Ds + kTB * LD, *Vs = Ks + kTB * LD, *Ps = Vs + kTB * LD;
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   const int g = blockIdx.y, b = g / p.H, h = g % p.H;
@@ -233,7 +280,8 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
   int hi = p.Lk;
   if (p.causal) hi = min(hi, m0 + kTB + p.shift);
 
-  float acc[8][NC], lse2[8], dl[8];
+  uint64_t acc[8][NC];
+  float lse2[8], dl[8];
   #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int r = m0 + ty + 8 * i;
@@ -246,7 +294,7 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
     }
     lse2[i] = ls;
     #pragma unroll
-    for (int c = 0; c < NC; ++c) acc[i][c] = 0.f;
+    for (int c = 0; c < NC; ++c) acc[i][c] = 0ull;
   }
   const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
   for (int n0 = 0; n0 < hi; n0 += kTB) {
@@ -260,8 +308,8 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
       #pragma unroll
       for (int j = 0; j < 4; ++j) { s[i][j] = 0.f; dp[i][j] = 0.f; }
     }
-    t_gemm_nt<DP>(Qs, Ks, ty, tx, s);
-    t_gemm_nt<DP>(Ds, Vs, ty, tx, dp);
+    t_gemm_nt<DP, true>(Qs, Ks, ty, tx, s);
+    t_gemm_nt<DP, true>(Ds, Vs, ty, tx, dp);
     #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = m0 + ty + 8 * i;
@@ -291,7 +339,7 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
                         const float *lse, const float *delta, View<T> dk, View<T> dv,
                         GenericParams p) {
   extern __shared__ __align__(16) float tsm[];
-  constexpr int LD = DP + 4, NC = DP / 16;
+  constexpr int LD = DP + 4, NC = DP / 32;
   float *Ks = tsm, *Vs = Ks + kTB * LD, *Qs = Vs + kTB * LD, *Ds = Qs + kTB * LD, *Ps = Ds + kTB * LD;
   float *lse2s = Ps + kTB * kTLdp, *dls = lse2s + kTB;
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
@@ -302,11 +350,11 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
   int m_start = 0;  // first query tile with a row that sees key n0+63... or any key of the tile
   if (p.causal) m_start = (max(0, n0 - p.shift) / kTB) * kTB;
 
-  float acck[8][NC], accv[8][NC];
+  uint64_t acck[8][NC], accv[8][NC];
   #pragma unroll
   for (int i = 0; i < 8; ++i) {
     #pragma unroll
-    for (int c = 0; c < NC; ++c) { acck[i][c] = 0.f; accv[i][c] = 0.f; }
+    for (int c = 0; c < NC; ++c) { acck[i][c] = 0ull; accv[i][c] = 0ull; }
   }
   const T *qslab = q.row(b, h, 0), *dslab = dout.row(b, h, 0);
   for (int m0 = m_start; m0 < p.Lq; m0 += kTB) {
@@ -330,8 +378,8 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
       #pragma unroll
       for (int j = 0; j < 4; ++j) { s[i][j] = 0.f; dp[i][j] = 0.f; }
     }
-    t_gemm_nt<DP>(Ks, Qs, ty, tx, s);    // s[i][j] = K[n0+ty+8i] . Q[m0+tx+16j]
-    t_gemm_nt<DP>(Vs, Ds, ty, tx, dp);
+    t_gemm_nt<DP, (DP < 128)>(Ks, Qs, ty, tx, s);    // s[i][j] = K[n0+ty+8i] . Q[m0+tx+16j]
+    t_gemm_nt<DP, (DP < 128)>(Vs, Ds, ty, tx, dp);
     #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int r = m0 + tx + 16 * j;
