@@ -304,16 +304,32 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   bp.causal = p->causal; bp.shift = p->q_pos0 - p->kv_pos0;
   bp.scale = p->softmax_scale; bp.scale_log2 = p->softmax_scale * fa::kLog2e;
   bp.num_kv_tiles = (p->Lk + 127) / 128;
-  auto kern = fa::fa_bwd_sm100_kernel<D, kBf16>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  const bool gqa = bp.kv_ratio > 1;
+  auto kern = gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false>;
+  static bool attr_set[2] = {false, false};
+  if (!attr_set[gqa]) {
     FA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     fa::BwdSmem<D>::kBytes));
-    attr_set = true;
+    attr_set[gqa] = true;
   }
   const unsigned grid = (unsigned)((int64_t)p->B * Hkv * bp.num_kv_tiles);  // one CTA per (batch, K/V head, KV tile)
+#ifdef FA_BWD_TRACE
+  static unsigned long long *d_btrace = nullptr;
+  if (!d_btrace) { cudaMalloc(&d_btrace, 16 * 8); }
+  cudaMemset(d_btrace, 0, 16 * 8);
+  bp.trace = d_btrace;
+#endif
   kern<<<grid, fa::kBwdThreads, fa::BwdSmem<D>::kBytes, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, bp);
   if (int rc = launched()) return rc;
+#ifdef FA_BWD_TRACE
+  if (D == 128 && p->Lq >= 8192) {
+    unsigned long long h[16];
+    cudaStreamSynchronize(st);
+    cudaMemcpy(h, d_btrace, sizeof(h), cudaMemcpyDeviceToHost);
+    fprintf(stderr, "bwd trace (CTA 0, MMA warp, clk per iteration): do_full %.0f dq_empty %.0f p_full %.0f q_full %.0f ds_full %.0f | loop %.0f (n=%llu)\n",
+            (double)h[0] / h[6], (double)h[1] / h[6], (double)h[2] / h[6], (double)h[3] / h[6], (double)h[4] / h[6], (double)h[5] / h[6], h[6]);
+  }
+#endif
   // dQ = softmax_scale * dq_acc, cast to the output dtype
   fa::fa_convert_kernel<T><<<148 * 8, 256, 0, st>>>(dq_acc, view<T>(dq), p->B, p->H, p->Lq, D,
                                                      p->softmax_scale);

@@ -42,6 +42,9 @@ struct BwdParams {
   int causal, shift;
   float scale, scale_log2;
   int num_kv_tiles;    // ceil(Lk / 128)
+#ifdef FA_BWD_TRACE
+  unsigned long long *trace;  // CTA 0: cycles the MMA warp spent in each of its waits
+#endif
 };
 
 template <int D>
@@ -68,7 +71,22 @@ __device__ __forceinline__ int bwd_first_q_tile(const BwdParams &p, int j) {
   return a <= 0 ? 0 : a / 128;
 }
 
-template <int D, bool kBf16>
+#ifdef FA_BWD_TRACE
+#define FA_BT_WAIT(slot, ...) do { const long long t0__ = clock64(); __VA_ARGS__; tr[slot] += clock64() - t0__; } while (0)
+#else
+#define FA_BT_WAIT(slot, ...) do { __VA_ARGS__; } while (0)
+#endif
+
+template <bool kGqa>
+__device__ __forceinline__ void bwd_next_tile(int &h, int &i, int i0, int num_q_tiles) {
+  ++i;
+  if (kGqa && i == num_q_tiles) { i = i0; ++h; }
+}
+
+// kGqa = several query heads share the CTA's K/V head (the Q-tile loop then walks head by head);
+// the multi-head instantiation keeps the plain induction variable i = i0 + it, which the compiler
+// holds in uniform registers (the loop-carried (h, i) pair cost 6 % of the backward).
+template <int D, bool kBf16, bool kGqa>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -103,8 +121,8 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   // The CTA walks the Q tiles of every query head that shares this K/V head (grouped-query
   // attention: kv_ratio heads; dK, dV simply keep accumulating in TMEM across them).
   const int n1 = max(num_q_tiles - i0, 0);     // Q tiles per query head
-  const int n = n1 * p.kv_ratio;               // loop iterations; iteration it -> head it / n1, tile it % n1
-  const int h0 = hk * p.kv_ratio;
+  const int n = kGqa ? n1 * p.kv_ratio : n1;   // loop iterations: heads outer, Q tiles i0.. inner
+  const int h0 = kGqa ? hk * p.kv_ratio : hk;
 
   if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) {
     printf("fa_b200: dynamic shared memory is not 1024-byte aligned\n");
@@ -137,8 +155,8 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tma_load_4d(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
         tma_load_4d(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
       }
-      for (int it = 0; it < n; ++it) {
-        const int h = h0 + it / n1, i = i0 + it % n1, s = it & 1;
+      for (int it = 0, h = h0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(h, i, i0, num_q_tiles)) {
+        const int s = it & 1;
         const float *lse_g = p.lse2 + static_cast<size_t>(b * p.H + h) * p.Lq_pad;
         const float *delta_g = p.delta + static_cast<size_t>(b * p.H + h) * p.Lq_pad;
         mbar_wait(&q_empty[s], ((it >> 1) & 1) ^ 1);
@@ -202,18 +220,22 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         issue_kk(tS, k_kmaj, q_kmaj);  // S^T(0)
         umma_commit(s_full);
       }
+#ifdef FA_BWD_TRACE
+      long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      const long long t_loop = clock64();
+#endif
       for (int it = 0; it < n; ++it) {
         const uint32_t q_stage = (it & 1) * kTile16;
         // dP^T(it) = V dO^T   (overwrites dQ(it-1): the drain must have emptied it)
-        mbar_wait(do_full, it & 1);
-        if (it > 0) mbar_wait(dq_empty, (it - 1) & 1);
+        FA_BT_WAIT(0, mbar_wait(do_full, it & 1));
+        if (it > 0) FA_BT_WAIT(1, mbar_wait(dq_empty, (it - 1) & 1));
         tc_fence_after();
         if (leader) {
           issue_kk(tDP, v_kmaj, do_kmaj);
           umma_commit(dp_full);
         }
         // dV += P^T dO
-        mbar_wait(p_full, it & 1);
+        FA_BT_WAIT(2, mbar_wait(p_full, it & 1));
         tc_fence_after();
         if (leader) {
           #pragma unroll
@@ -224,7 +246,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         // S^T(it+1) = K Q^T  (overwrites P^T(it), which dV(it) has consumed by then: in-order pipe)
         if (it + 1 < n) {
-          mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
+          FA_BT_WAIT(3, mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1));
           tc_fence_after();
           if (leader) {
             issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16);
@@ -232,7 +254,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
         }
         // dQ(it) = dS K ; dK += dS^T Q
-        mbar_wait(ds_full, it & 1);
+        FA_BT_WAIT(4, mbar_wait(ds_full, it & 1));
         tc_fence_after();
         if (leader) {
           #pragma unroll
@@ -250,6 +272,13 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         __syncwarp();
       }
       if (leader) umma_commit(dkv_full);
+#ifdef FA_BWD_TRACE
+      if (blockIdx.x == 0 && lane == 0) {
+        for (int t = 0; t < 5; ++t) p.trace[t] = tr[t];
+        p.trace[5] = clock64() - t_loop;
+        p.trace[6] = n;
+      }
+#endif
       (void)kHalf16;
     }
   } else if (warp >= 8 && warp < 12) {
@@ -261,40 +290,47 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int w = warp & 3;
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
     uint8_t *wstage = smem + L::kDQOff + w * 8192;
-    for (int it = 0; it < n; ++it) {
-      const int h = h0 + it / n1, i = i0 + it % n1;
+    for (int it = 0, h = h0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(h, i, i0, num_q_tiles)) {
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
+      // 64 fp32 columns (two 32-column slabs, one per staging buffer) at a time.  The TMEM reads of
+      // the next half are issued as soon as this half's registers have been stored, so dQ leaves
+      // TMEM (dq_empty -> the MMA warp may overwrite it with dP^T(it+1)) after two loads, one
+      // round of stores and no wait on the reduce engine.
+      uint32_t r[2][32];
+      tmem_ld32(tDQ, r[0]);
+      tmem_ld32(tDQ + 32, r[1]);
       #pragma unroll
-      for (int hh = 0; hh < kHalves; ++hh) {  // 64 fp32 columns (two 32-column slabs) at a time
-        uint32_t r[2][32];
-        tmem_ld32(tDQ + hh * 64, r[0]);
-        tmem_ld32(tDQ + hh * 64 + 32, r[1]);
+      for (int hh = 0; hh < kHalves; ++hh) {
         tmem_ld_wait();
         if (hh == kHalves - 1) { tc_fence_before(); mbar_arrive_warp(dq_empty); }
+        if (lane == 0) tma_store_wait_read<0>();  // the reduces that last used the two buffers have read them
+        __syncwarp();
+#ifndef FA_EXPERIMENT_NO_DRAIN_STS  // (timing experiment only when defined: wrong results)
         #pragma unroll
         for (int sl = 0; sl < 2; ++sl) {
-          uint8_t *buf = wstage + sl * 4096;
-          if (lane == 0) tma_store_wait_read<1>();  // the reduce that last used this buffer has read it
-          __syncwarp();
-#ifdef FA_EXPERIMENT_NO_DRAIN_STS  // timing experiment only (wrong results)
-          asm volatile("" ::"r"(r[sl][0]), "r"(r[sl][31]));
-          continue;
-#endif
           #pragma unroll
           for (int c = 0; c < 8; ++c) {
             uint4 v4 = make_uint4(r[sl][c * 4], r[sl][c * 4 + 1], r[sl][c * 4 + 2], r[sl][c * 4 + 3]);
-            *reinterpret_cast<uint4 *>(buf + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
+            *reinterpret_cast<uint4 *>(wstage + sl * 4096 + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
           }
-          fence_proxy_async_smem();
-          __syncwarp();
-#ifndef FA_EXPERIMENT_NO_REDUCE
-          if (lane == 0) {
-            tma_reduce_add_4d(&tmDQ, buf, hh * 64 + sl * 32, i * 128 + w * 32, h, b);
-            tma_store_commit();
-          }
-#endif
         }
+#else
+        asm volatile("" ::"r"(r[0][0]), "r"(r[1][31]));
+#endif
+        if (hh + 1 < kHalves) {
+          tmem_ld32(tDQ + (hh + 1) * 64, r[0]);
+          tmem_ld32(tDQ + (hh + 1) * 64 + 32, r[1]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+#if !defined(FA_EXPERIMENT_NO_REDUCE) && !defined(FA_EXPERIMENT_NO_DRAIN_STS)
+        if (lane == 0) {
+          tma_reduce_add_4d(&tmDQ, wstage, hh * 64, i * 128 + w * 32, h, b);
+          tma_reduce_add_4d(&tmDQ, wstage + 4096, hh * 64 + 32, i * 128 + w * 32, h, b);
+          tma_store_commit();
+        }
+#endif
       }
     }
     if (lane == 0) tma_store_wait<0>();
@@ -309,8 +345,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     uint8_t *ds_row = smem + L::kDSOff + wg * L::kHalfBytes + row * 128;
     const int key = j * 128 + row;
 
-    for (int it = 0; it < n; ++it) {
-      const int i = i0 + it % n1;
+    for (int it = 0, hx = 0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(hx, i, i0, num_q_tiles)) {
       const float4 *stat = reinterpret_cast<const float4 *>(smem + L::kStatOff + (it & 1) * 1024) + wg * 16;
       mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
       // -lse2 of this warpgroup's 64 query columns: loaded (broadcast LDS.128) BEFORE the S^T wait so
