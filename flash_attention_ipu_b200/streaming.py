@@ -55,8 +55,9 @@ class HostStreamedAttention:
             s = c % 2
             if c < self.n:  # ---- upload chunk c
                 with torch.cuda.stream(self.s_in):
-                    if c >= 2:
-                        self.s_in.wait_event(self.ev_free[s])
+                    # the staging buffer's previous user (two chunks back, possibly the tail of the
+                    # previous run) must have consumed it; a never-recorded event is a no-op
+                    self.s_in.wait_event(self.ev_free[s])
                     sl = slice(c * gc, (c + 1) * gc)
                     for i in range(3):  # each [i, sl] is one contiguous block on the host
                         self.d_qkv[s][i].copy_(h_qkv[i, sl], non_blocking=True)
