@@ -142,15 +142,30 @@ int allow_smem(K kernel, size_t bytes) {
   return 0;
 }
 
-template <typename T, int DP>
-int tiled_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
-              const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
-  auto kern = fa::fa_tiled_fwd_kernel<T, DP>;
+// cp.async staging needs fp32 rows whose every 4-element group is 16-byte aligned
+bool rows_16b(const fa_b200_tensor *t) {
+  return reinterpret_cast<uintptr_t>(t->ptr) % 16 == 0 && t->stride_l % 4 == 0 && t->stride_h % 4 == 0 &&
+         t->stride_b % 4 == 0;
+}
+
+template <typename T, int DP, bool kAsync>
+int tiled_fwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                     const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  auto kern = fa::fa_tiled_fwd_kernel<T, DP, kAsync>;
   static int once = allow_smem(kern, fa::t_fwd_smem<DP>());
   if (once) return once;
   kern<<<dim3(tiles(p->Lq), (unsigned)(p->B * p->H)), fa::kTThreads, fa::t_fwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<T>(o), lse, gparams(p));
   return launched();
+}
+
+template <typename T, int DP>
+int tiled_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+              const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  if constexpr (std::is_same<T, float>::value) {
+    if (p->D % 4 == 0 && rows_16b(k) && rows_16b(v)) return tiled_fwd_launch<T, DP, true>(p, q, k, v, o, lse, st);
+  }
+  return tiled_fwd_launch<T, DP, false>(p, q, k, v, o, lse, st);
 }
 
 template <typename T>
@@ -174,13 +189,13 @@ int launch_delta(const fa_b200_problem *p, const fa_b200_tensor *o, const fa_b20
   return launched();
 }
 
-template <typename T, int DP>
-int tiled_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
-              const fa_b200_tensor *v, const fa_b200_tensor *dout, const float *lse,
-              const fa_b200_tensor *dq, const fa_b200_tensor *dk, const fa_b200_tensor *dv,
-              const float *delta, cudaStream_t st) {
-  auto kq = fa::fa_tiled_bwd_dq_kernel<T, DP>;
-  auto kkv = fa::fa_tiled_bwd_dkv_kernel<T, DP>;
+template <typename T, int DP, bool kAsync>
+int tiled_bwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                     const fa_b200_tensor *v, const fa_b200_tensor *dout, const float *lse,
+                     const fa_b200_tensor *dq, const fa_b200_tensor *dk, const fa_b200_tensor *dv,
+                     const float *delta, cudaStream_t st) {
+  auto kq = fa::fa_tiled_bwd_dq_kernel<T, DP, kAsync>;
+  auto kkv = fa::fa_tiled_bwd_dkv_kernel<T, DP, kAsync>;
   static int once = [&] { int rc = allow_smem(kq, fa::t_bwd_smem<DP>()); return rc ? rc : allow_smem(kkv, fa::t_bwd_smem<DP>()); }();
   if (once) return once;
   const unsigned groups = (unsigned)(p->B * p->H);
@@ -192,6 +207,18 @@ int tiled_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_t
       view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
       view<T>(dk), view<T>(dv), gparams(p));
   return launched();
+}
+
+template <typename T, int DP>
+int tiled_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+              const fa_b200_tensor *v, const fa_b200_tensor *dout, const float *lse,
+              const fa_b200_tensor *dq, const fa_b200_tensor *dk, const fa_b200_tensor *dv,
+              const float *delta, cudaStream_t st) {
+  if constexpr (std::is_same<T, float>::value) {
+    if (p->D % 4 == 0 && rows_16b(q) && rows_16b(k) && rows_16b(v) && rows_16b(dout))
+      return tiled_bwd_launch<T, DP, true>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
+  }
+  return tiled_bwd_launch<T, DP, false>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
 }
 
 template <typename T>

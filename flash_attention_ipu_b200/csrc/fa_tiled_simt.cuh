@@ -67,6 +67,40 @@ __device__ __forceinline__ void t_load_tile(float *dst, const T *slab, int64_t s
   }
 }
 
+__device__ __forceinline__ void t_cp_async_16(float *smem_dst, const float *gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void t_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void t_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
+
+// A streamed tile (unscaled).  kAsync (fp32 rows, 16-byte aligned): cp.async straight into shared
+// memory, one commit group per tile -- the copy lands while the caller runs a product on the
+// other operand; otherwise the synchronous converting load.  The kernels' barrier structure is
+// written for the asynchronous form and is also correct for the synchronous one.
+template <typename T, int DP, bool kAsync>
+__device__ __forceinline__ void t_stream_tile(float *dst, const T *slab, int64_t sl, int row0, int nrows, int D) {
+  if constexpr (kAsync) {
+    static_assert(sizeof(T) == 4, "cp.async staging is for fp32 inputs");
+    constexpr int LD = DP + 4, V4 = DP / 4;
+    #pragma unroll 4
+    for (int idx = threadIdx.x; idx < kTB * V4; idx += kTThreads) {
+      const int r = idx / V4, d = (idx % V4) * 4;
+      float *to = dst + r * LD + d;
+      const int gr = row0 + r;
+      if (gr < nrows && d < D) t_cp_async_16(to, reinterpret_cast<const float *>(slab) + gr * sl + d);
+      else *reinterpret_cast<float4 *>(to) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    t_cp_async_commit();
+  } else {
+    t_load_tile<T, DP>(dst, slab, sl, row0, nrows, D, 1.f);
+  }
+}
+template <bool kAsync, int kPending>
+__device__ __forceinline__ void t_stream_wait() {
+  if constexpr (kAsync) t_cp_async_wait<kPending>();
+}
+
 // c[i][j] += sum_d A[ty + 8 i][d] * B[tx + 16 j][d].  kPacked: FFMA2 over (even d, odd d) partial
 // sums (64 transient accumulator registers); otherwise scalar FFMA (32), for the register-bound
 // dK/dV kernel at DP = 128.
@@ -184,7 +218,7 @@ template <int DP> constexpr size_t t_bwd_smem() { return (4 * kTB * (DP + 4) + k
 
 // ------------------------------------------------------------------ forward
 // grid (query tiles, B*H).  Q tile stationary (scaled by softmax_scale * log2 e), K/V streamed.
-template <typename T, int DP>
+template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
 fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o, float *lse,
                     GenericParams p) {
@@ -207,15 +241,19 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
     for (int c = 0; c < NC; ++c) acc[i][c] = 0ull;
   }
   const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
+  // K(n) is fetched while P(n-1) V(n-1) runs, V(n) while Q K(n)^T runs.
+  if (hi > 0) t_stream_tile<T, DP, kAsync>(Ks, kslab, k.sl, 0, p.Lk, p.D);
   for (int n0 = 0; n0 < hi; n0 += kTB) {
-    __syncthreads();  // everyone is done with the previous K/V tile
-    t_load_tile<T, DP>(Ks, kslab, k.sl, n0, p.Lk, p.D, 1.f);
-    t_load_tile<T, DP>(Vs, vslab, v.sl, n0, p.Lk, p.D, 1.f);
-    __syncthreads();
+    t_stream_wait<kAsync, 0>();
+    __syncthreads();  // K(n0) has landed; everyone is done with the previous V tile
+    t_stream_tile<T, DP, kAsync>(Vs, vslab, v.sl, n0, p.Lk, p.D);
     float s[8][4];
     #pragma unroll
     for (int i = 0; i < 8; ++i) { s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f; }
     t_gemm_nt<DP, true>(Qs, Ks, ty, tx, s);
+    __syncthreads();  // everyone is done with K(n0)
+    const bool has_next = n0 + kTB < hi;
+    if (has_next) t_stream_tile<T, DP, kAsync>(Ks, kslab, k.sl, n0 + kTB, p.Lk, p.D);
     const bool edge = (n0 + kTB > p.Lk) || (p.causal && n0 + kTB - 1 > m0 + p.shift);
     if (edge) {
       #pragma unroll
@@ -247,7 +285,8 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
       #pragma unroll
       for (int c = 0; c < NC; ++c) acc[i][c] = f2_mul(acc[i][c], cc2);
     }
-    __syncwarp();
+    if (has_next) t_stream_wait<kAsync, 1>(); else t_stream_wait<kAsync, 0>();  // V(n0); K(next) may be in flight
+    __syncthreads();
     t_gemm_nn<DP>(Ps, Vs, ty, tx, acc);
   }
   float inv[8];
@@ -265,7 +304,7 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
 // ------------------------------------------------------------------ backward: dQ
 // grid (query tiles, B*H).  Q (scaled) and dO stationary, K/V streamed.
 // P = exp(S - LSE) (:457-459); dP = dO V^T (:465); dS = P (dP - delta) (:466-467); dQ += dS K (:470)
-template <typename T, int DP>
+template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
 fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<const T> dout,
                        const float *lse, const float *delta, View<T> dq, GenericParams p) {
@@ -297,19 +336,23 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
     for (int c = 0; c < NC; ++c) acc[i][c] = 0ull;
   }
   const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
+  // V(n) is fetched while Q K(n-1)^T and dS K(n-1) run, K(n) while dO V(n)^T runs.
+  if (hi > 0) t_stream_tile<T, DP, kAsync>(Vs, vslab, v.sl, 0, p.Lk, p.D);
   for (int n0 = 0; n0 < hi; n0 += kTB) {
-    __syncthreads();
-    t_load_tile<T, DP>(Ks, kslab, k.sl, n0, p.Lk, p.D, 1.f);
-    t_load_tile<T, DP>(Vs, vslab, v.sl, n0, p.Lk, p.D, 1.f);
-    __syncthreads();
+    t_stream_wait<kAsync, 0>();
+    __syncthreads();  // V(n0) has landed; everyone is done with the previous K tile
+    t_stream_tile<T, DP, kAsync>(Ks, kslab, k.sl, n0, p.Lk, p.D);
     float s[8][4], dp[8][4];
     #pragma unroll
     for (int i = 0; i < 8; ++i) {
       #pragma unroll
       for (int j = 0; j < 4; ++j) { s[i][j] = 0.f; dp[i][j] = 0.f; }
     }
-    t_gemm_nt<DP, true>(Qs, Ks, ty, tx, s);
     t_gemm_nt<DP, true>(Ds, Vs, ty, tx, dp);
+    t_stream_wait<kAsync, 0>();
+    __syncthreads();  // K(n0) has landed; everyone is done with V(n0)
+    if (n0 + kTB < hi) t_stream_tile<T, DP, kAsync>(Vs, vslab, v.sl, n0 + kTB, p.Lk, p.D);
+    t_gemm_nt<DP, true>(Qs, Ks, ty, tx, s);
     #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = m0 + ty + 8 * i;
@@ -333,7 +376,7 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
 // ------------------------------------------------------------------ backward: dK, dV
 // grid (key tiles, B*H).  K (scaled) and V stationary, Q/dO streamed; the score tile is held
 // transposed (rows = keys) so that dV += P^T dO (:462) and dK += dS^T Q (:472) are NN products.
-template <typename T, int DP>
+template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
 fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<const T> dout,
                         const float *lse, const float *delta, View<T> dk, View<T> dv,
@@ -357,10 +400,12 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
     for (int c = 0; c < NC; ++c) { acck[i][c] = 0ull; accv[i][c] = 0ull; }
   }
   const T *qslab = q.row(b, h, 0), *dslab = dout.row(b, h, 0);
+  // dO(m) is fetched while dS^T Q(m-1) runs, Q(m) while V dO(m)^T runs.
+  if (m_start < p.Lq) t_stream_tile<T, DP, kAsync>(Ds, dslab, dout.sl, m_start, p.Lq, p.D);
   for (int m0 = m_start; m0 < p.Lq; m0 += kTB) {
-    __syncthreads();
-    t_load_tile<T, DP>(Qs, qslab, q.sl, m0, p.Lq, p.D, 1.f);
-    t_load_tile<T, DP>(Ds, dslab, dout.sl, m0, p.Lq, p.D, 1.f);
+    t_stream_wait<kAsync, 0>();
+    __syncthreads();  // dO(m0) has landed; everyone is done with the previous Q tile and its stats
+    t_stream_tile<T, DP, kAsync>(Qs, qslab, q.sl, m0, p.Lq, p.D);
     if (tid < kTB) {
       const int r = m0 + tid;
       float ls = INFINITY, dl = 0.f;
@@ -371,15 +416,16 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
       }
       lse2s[tid] = ls; dls[tid] = dl;
     }
-    __syncthreads();
     float s[8][4], dp[8][4];
     #pragma unroll
     for (int i = 0; i < 8; ++i) {
       #pragma unroll
       for (int j = 0; j < 4; ++j) { s[i][j] = 0.f; dp[i][j] = 0.f; }
     }
-    t_gemm_nt<DP, (DP < 128)>(Ks, Qs, ty, tx, s);    // s[i][j] = K[n0+ty+8i] . Q[m0+tx+16j]
     t_gemm_nt<DP, (DP < 128)>(Vs, Ds, ty, tx, dp);
+    t_stream_wait<kAsync, 0>();
+    __syncthreads();  // Q(m0) and the row statistics are visible
+    t_gemm_nt<DP, (DP < 128)>(Ks, Qs, ty, tx, s);    // s[i][j] = K[n0+ty+8i] . Q[m0+tx+16j]
     #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int r = m0 + tx + 16 * j;
@@ -400,7 +446,8 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
     }
     __syncwarp();
     t_gemm_nn<DP>(Ps, Ds, ty, tx, accv);
-    __syncwarp();
+    __syncthreads();  // everyone is done with dO(m0) (and with P^T in Ps)
+    if (m0 + kTB < p.Lq) t_stream_tile<T, DP, kAsync>(Ds, dslab, dout.sl, m0 + kTB, p.Lq, p.D);
     #pragma unroll
     for (int i = 0; i < 8; ++i) {
       #pragma unroll
