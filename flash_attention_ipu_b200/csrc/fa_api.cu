@@ -191,17 +191,17 @@ int launch_delta(const fa_b200_problem *p, const fa_b200_tensor *o, const fa_b20
 
 template <typename T, int DP, bool kAsync>
 int tiled_bwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
-                     const fa_b200_tensor *v, const fa_b200_tensor *dout, const float *lse,
-                     const fa_b200_tensor *dq, const fa_b200_tensor *dk, const fa_b200_tensor *dv,
-                     const float *delta, cudaStream_t st) {
+                     const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                     const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+                     const fa_b200_tensor *dv, float *delta, cudaStream_t st) {
   auto kq = fa::fa_tiled_bwd_dq_kernel<T, DP, kAsync>;
   auto kkv = fa::fa_tiled_bwd_dkv_kernel<T, DP, kAsync>;
   static int once = [&] { int rc = allow_smem(kq, fa::t_bwd_smem<DP>()); return rc ? rc : allow_smem(kkv, fa::t_bwd_smem<DP>()); }();
   if (once) return once;
   const unsigned groups = (unsigned)(p->B * p->H);
   kq<<<dim3(tiles(p->Lq), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
-      view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
-      view<T>(dq), gparams(p));
+      view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(o), view<const T>(dout), lse,
+      delta, view<T>(dq), gparams(p));  // also writes delta for the next kernel
   if (int rc = launched()) return rc;
   kkv<<<dim3(tiles(p->Lk), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
@@ -211,14 +211,14 @@ int tiled_bwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa
 
 template <typename T, int DP>
 int tiled_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
-              const fa_b200_tensor *v, const fa_b200_tensor *dout, const float *lse,
-              const fa_b200_tensor *dq, const fa_b200_tensor *dk, const fa_b200_tensor *dv,
-              const float *delta, cudaStream_t st) {
+              const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+              const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+              const fa_b200_tensor *dv, float *delta, cudaStream_t st) {
   if constexpr (std::is_same<T, float>::value) {
     if (p->D % 4 == 0 && rows_16b(q) && rows_16b(k) && rows_16b(v) && rows_16b(dout))
-      return tiled_bwd_launch<T, DP, true>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
+      return tiled_bwd_launch<T, DP, true>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
   }
-  return tiled_bwd_launch<T, DP, false>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
+  return tiled_bwd_launch<T, DP, false>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
 }
 
 template <typename T>
@@ -226,9 +226,9 @@ int generic_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
                 const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
                 const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
                 const fa_b200_tensor *dv, float *delta, cudaStream_t st) {
+  if (p->D <= 64) return tiled_bwd<T, 64>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
+  if (p->D <= 128) return tiled_bwd<T, 128>(p, q, k, v, o, dout, lse, dq, dk, dv, delta, st);
   if (int rc = launch_delta<T>(p, o, dout, delta, st)) return rc;
-  if (p->D <= 64) return tiled_bwd<T, 64>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
-  if (p->D <= 128) return tiled_bwd<T, 128>(p, q, k, v, dout, lse, dq, dk, dv, delta, st);
   const int64_t qrows = (int64_t)p->B * p->H * p->Lq, krows = (int64_t)p->B * p->H * p->Lk;
   const size_t sm = fa::kGenWarps * 2 * p->D * sizeof(float);
   fa::fa_generic_bwd_dq_kernel<T><<<blocks_for(qrows, fa::kGenWarps), fa::kGenWarps * 32, sm, st>>>(

@@ -306,8 +306,8 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
 // P = exp(S - LSE) (:457-459); dP = dO V^T (:465); dS = P (dP - delta) (:466-467); dQ += dS K (:470)
 template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
-fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<const T> dout,
-                       const float *lse, const float *delta, View<T> dq, GenericParams p) {
+fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<const T> o,
+                       View<const T> dout, const float *lse, float *delta, View<T> dq, GenericParams p) {
   extern __shared__ __align__(16) float tsm[];
   constexpr int LD = DP + 4, NC = DP / 32;
   float *Qs = tsm, *Ds = Qs + kTB * LD, *Ks = Ds + kTB * LD, *Vs = Ks + kTB * LD, *Ps = Vs + kTB * LD;
@@ -325,12 +325,24 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
   for (int i = 0; i < 8; ++i) {
     const int r = m0 + ty + 8 * i;
     float ls = INFINITY;  // exp2(s - inf) = 0: rows that saw no key, rows past the end
-    dl[i] = 0.f;
+    // delta = rowsum(O o dO) (:374-377) is computed here, 16 lanes per row, and written out for
+    // the dK/dV kernel that follows on the stream -- no separate pass over O and dO
+    float part = 0.f;
     if (r < p.Lq) {
       const float x = lse[static_cast<int64_t>(g) * p.Lq + r];
       if (x > -INFINITY) ls = x * kTLog2e;
-      dl[i] = delta[static_cast<int64_t>(g) * p.Lq + r];
+      const T *orow = o.row(b, h, r), *drow = dout.row(b, h, r);
+      #pragma unroll
+      for (int jj = 0; jj < DP / 64; ++jj) {
+        #pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int d = tx * 4 + 64 * jj + e;
+          if (d < p.D) part = fmaf(to_f32(orow[d]), to_f32(drow[d]), part);
+        }
+      }
     }
+    dl[i] = t_sum16(part);
+    if (tx == 0 && r < p.Lq) delta[static_cast<int64_t>(g) * p.Lq + r] = dl[i];
     lse2[i] = ls;
     #pragma unroll
     for (int c = 0; c < NC; ++c) acc[i][c] = 0ull;
