@@ -413,3 +413,34 @@ def test_tiled_simt_kernels(B, H, Lq, Lk, D, causal, q0, k0, dtype):
     assert (lse.cpu().double()[fin] - ref[1][fin]).abs().max().item() <= (1e-4 if dtype == "fp32" else 1e-2)
     for got, want in zip((o, dq, dk, dv), (ref[0], ref[2], ref[3], ref[4])):
         assert (got.cpu().double() - want).abs().max().item() <= atol
+
+
+def test_config1_full_size_fp32():
+    """BASELINE config 1 at its full size (B=64, T=256, 6 heads, d=64, fp32, causal), as nanoGPT
+    calls it (strided views of one c_attn output), against torch CPU SDPA in fp32."""
+    import torch.nn.functional as F
+    import flash_attention_ipu_b200._impl.scaled_dot_product_attention as mod
+    native = _native_loaded()
+    B, T, nh, hs = 64, 256, 6, 64
+    torch.manual_seed(SEED)
+    c_attn = torch.randn(B, T, 3 * nh * hs)
+    dout = torch.randn(B, nh, T, hs)
+    xr = c_attn.clone().requires_grad_(True)
+    q, k, v = (t.view(B, T, nh, hs).transpose(1, 2) for t in xr.split(nh * hs, dim=2))
+    ref = ao.sdpa_reference(q, k, v)
+    (ref * dout).sum().backward()
+    was = getattr(F.scaled_dot_product_attention, "__wrapped__", None) is not None
+    mod.install()
+    try:
+        before = native.launch_count()
+        x = c_attn.cuda().requires_grad_(True)
+        q, k, v = (t.view(B, T, nh, hs).transpose(1, 2) for t in x.split(nh * hs, dim=2))
+        out = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        out.backward(dout.cuda())
+        torch.cuda.synchronize()
+        assert native.launch_count() - before == 3  # forward, dQ (+delta), dK/dV
+    finally:
+        if not was:
+            mod.uninstall()
+    assert (out.detach().cpu() - ref.detach()).abs().max().item() <= 2e-5
+    assert (x.grad.cpu() - xr.grad).abs().max().item() <= 1e-4
