@@ -75,7 +75,7 @@ def corpus(device):
 
 def train(patched: bool, steps: int, n_layer: int, batch: int, block: int, n_head: int, n_embd: int,
           dtype=torch.bfloat16, seed: int = 1123581321):
-    """One training run; returns (losses, peak_bytes, attention kernel launches)."""
+    """One training run; returns (losses, peak_bytes, attention kernel launches, ms per step)."""
     from flash_attention_ipu_b200._impl import native
     from flash_attention_ipu_b200._impl import scaled_dot_product_attention as sd  # importing it patches
     was_patched = hasattr(F.scaled_dot_product_attention, "__wrapped__")
@@ -88,7 +88,10 @@ def train(patched: bool, steps: int, n_layer: int, batch: int, block: int, n_hea
     gen = torch.Generator(device="cpu").manual_seed(seed)
     torch.cuda.reset_peak_memory_stats()
     launches0, losses = native.launch_count(), []
-    for _ in range(steps):
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for it in range(steps):
+        if it == steps // 2:
+            t_start.record()  # second half only: allocator and autotuning have settled
         ix = torch.randint(len(data) - block - 1, (batch,), generator=gen)
         x = torch.stack([data[i:i + block] for i in ix])
         y = torch.stack([data[i + 1:i + 1 + block] for i in ix])
@@ -99,8 +102,11 @@ def train(patched: bool, steps: int, n_layer: int, batch: int, block: int, n_hea
         torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
         losses.append(loss.item())
+    t_end.record()
+    torch.cuda.synchronize()
+    ms = t_start.elapsed_time(t_end) / max(1, steps - steps // 2)
     (sd.install if was_patched else sd.uninstall)()  # leave the override as it was found
-    return losses, torch.cuda.max_memory_allocated(), native.launch_count() - launches0
+    return losses, torch.cuda.max_memory_allocated(), native.launch_count() - launches0, ms
 
 
 def main():
@@ -111,15 +117,15 @@ def main():
     ap.add_argument("--block", type=int, default=256)
     args = ap.parse_args()
     kw = dict(steps=args.steps, n_layer=args.layers, batch=args.batch, block=args.block, n_head=6, n_embd=384)
-    base, mem0, l0 = train(False, **kw)
-    ours, mem1, l1 = train(True, **kw)
+    base, mem0, l0, ms0 = train(False, **kw)
+    ours, mem1, l1, ms1 = train(True, **kw)
     k = max(1, args.steps // 10)
     print(json.dumps({
         "config": kw, "loss_unpatched": [round(sum(base[i:i + k]) / k, 4) for i in range(0, args.steps, k)],
         "loss_flash_attention_b200": [round(sum(ours[i:i + k]) / k, 4) for i in range(0, args.steps, k)],
         "max_abs_loss_gap": max(abs(a - b) for a, b in zip(base, ours)),
         "final_loss": [base[-1], ours[-1]], "ln_vocab": math.log(corpus(torch.device("cuda"))[1]),
-        "peak_mem_mb": [mem0 / 2 ** 20, mem1 / 2 ** 20], "attention_kernel_launches": [l0, l1]}))
+        "peak_mem_mb": [mem0 / 2 ** 20, mem1 / 2 ** 20], "ms_per_train_step": [ms0, ms1], "attention_kernel_launches": [l0, l1]}))
 
 
 if __name__ == "__main__":

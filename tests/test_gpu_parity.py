@@ -297,8 +297,8 @@ def test_nanogpt_demo_loss_curve_parity():
     demo = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(demo)
     kw = dict(steps=40, n_layer=2, batch=16, block=256, n_head=6, n_embd=384)
-    base, _, l0 = demo.train(False, **kw)
-    ours, _, l1 = demo.train(True, **kw)
+    base, _, l0, _ = demo.train(False, **kw)
+    ours, _, l1, _ = demo.train(True, **kw)
     assert l0 == 0 and l1 >= 2 * 2 * 40          # fwd + bwd (+ prep/convert) per layer per step
     assert ours[-1] < ours[0] - 0.5               # it learns
     assert max(abs(a - b) for a, b in zip(base[:10], ours[:10])) <= 0.1    # same curve (bf16 training noise is ~0.04)
