@@ -1,5 +1,5 @@
 #!/bin/bash
-# N-GPU check + bench of the NCCL ring (config 5).  usage: gpurun --gpus N -- ./gpu_ring.sh N
+# N-GPU check + bench of the NCCL ring (config 5).  usage: gpurun --gpus N -- ./scripts/gpu_ring.sh N
 N=${1:-2}
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29544"

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Multi-GPU check of the NCCL ring (run by hand / by gpu_ring.sh, not collected by pytest):
+"""Multi-GPU check of the NCCL ring (run by hand / by scripts/gpu_ring.sh, not collected by pytest):
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port 29544 tests/ring_nccl_check.py [T]

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Text summary of one `ncu --set full` report (the lines profiles/*.txt hold): usage
-   tools_ncu_summary.py report.ncu-rep > profiles/rNN_xxx.txt"""
+   tools/ncu_summary.py report.ncu-rep > profiles/rNN_xxx.txt"""
 import csv, subprocess, sys
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
