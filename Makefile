@@ -9,12 +9,22 @@ NVFLAGS ?= -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-Wall -Xptxas -v
 CSRC    := flash_attention_ipu_b200/csrc
 HDRS    := $(wildcard $(CSRC)/*.cuh) include/fa_b200.h
 
-all: $(OUT)/libflash_attention.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe $(OUT)/umma_rate $(OUT)/exp_rate
+all: $(OUT)/libflash_attention.so $(OUT)/libfa_torch_ops.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe $(OUT)/umma_rate $(OUT)/exp_rate
 
 $(OUT)/libflash_attention.so: $(CSRC)/fa_api.cu $(HDRS)
 	@mkdir -p $(OUT)
 	$(NVCC) $(NVFLAGS) -shared -o $@ $< 2> $(OUT)/ptxas_fa_api.log || (cat $(OUT)/ptxas_fa_api.log; false)
 	@grep -E "error|spill" $(OUT)/ptxas_fa_api.log | sort | uniq -c | head -20 || true
+
+# the torch.library ops (schema, autograd, CUDA implementation over the C ABI), plain g++: no kernels
+PYTHON    ?= python
+TORCH_INC := $(shell $(PYTHON) -c "import torch.utils.cpp_extension as c; print(' '.join('-isystem ' + p for p in c.include_paths()))" 2>/dev/null)
+TORCH_LIB := $(shell $(PYTHON) -c "import os, torch; print(os.path.join(os.path.dirname(torch.__file__), 'lib'))" 2>/dev/null)
+CUDA_HOME ?= /usr/local/cuda
+$(OUT)/libfa_torch_ops.so: $(CSRC)/torch_ops.cpp include/fa_b200.h $(OUT)/libflash_attention.so
+	g++ -std=c++17 -O2 -fPIC -shared -Wall -D_GLIBCXX_USE_CXX11_ABI=1 $(TORCH_INC) -isystem $(CUDA_HOME)/include \
+	    -o $@ $< -L$(OUT) -lflash_attention -L$(TORCH_LIB) -ltorch -ltorch_cpu -lc10 -lc10_cuda \
+	    -Wl,-rpath,'$$ORIGIN' -Wl,-rpath,$(TORCH_LIB)
 
 # the CPU oracle (test infrastructure, never linked into the product library)
 $(OUT)/liboracle.so: oracle/vanilla_attention.c

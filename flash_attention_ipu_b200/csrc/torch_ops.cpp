@@ -1,0 +1,251 @@
+// torch_ops.cpp -- the torch.library ops of the package, registered from C++ over the C ABI.
+//
+// Stand-in for the reference's popart plugin types (Op / GradOp / Opx / GradOpx / OpCreator,
+// flash_attention_ipu/cpp/flash_attention_qkv_packed.cpp:516-676): op definition + shape rules
+// (:571-577, :530), autodiff wiring (:536-546, :579-583) and lowering (:633-657) -- here: schema,
+// CUDA implementation that fills fa_b200_problem / fa_b200_tensor and calls fa_b200_fwd / _bwd
+// (include/fa_b200.h), and an autograd function.  Registered natively (not through Python's
+// torch.library.custom_op) because that layer costs ~65 us of host time per forward+backward
+// pair, which is what the small shapes (nanoGPT demo, GPT-2 small) are bound by.
+//
+// Autograd contract: forward returns (out, lse) and saves them; the reference's grad op
+// receives only (dOut, qkv) and re-runs the forward (:357-359, :536-541) -- not replicated.
+//
+// Links against libflash_attention.so only through the C ABI; no kernels in this file.
+#include <ATen/ATen.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <torch/csrc/autograd/custom_function.h>
+#include <torch/library.h>
+
+#include <tuple>
+
+#include "../../include/fa_b200.h"
+
+namespace {
+
+using at::Tensor;
+
+int dtype_code(const Tensor &t) {
+  switch (t.scalar_type()) {
+    case at::kHalf: return FA_B200_F16;
+    case at::kBFloat16: return FA_B200_BF16;
+    case at::kFloat: return FA_B200_F32;
+    default: TORCH_CHECK(false, "unsupported dtype ", t.scalar_type());
+  }
+  return -1;
+}
+
+void require_cuda(std::initializer_list<const Tensor *> ts) {
+  for (const Tensor *t : ts)
+    TORCH_CHECK(t->is_cuda(),
+                "flash_attention_ipu_b200 runs on CUDA (sm_100a) tensors only; there is no CPU path");
+}
+
+// (B,H,L,D) view the kernels can address in place: unit stride on D, 16-byte aligned base and
+// strides (the TMA path); anything else is made contiguous.
+Tensor as_bhld(const Tensor &t) {
+  const int64_t es = t.element_size();
+  bool ok = t.stride(-1) == 1 && reinterpret_cast<uintptr_t>(t.data_ptr()) % 16 == 0;
+  for (int64_t i = 0; ok && i + 1 < t.dim(); ++i) ok = (t.stride(i) * es) % 16 == 0;
+  return ok ? t : t.contiguous();
+}
+
+fa_b200_tensor desc(const Tensor &t) { return fa_b200_tensor{t.data_ptr(), t.stride(0), t.stride(1), t.stride(2)}; }
+
+fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, double scale, int64_t block_q,
+                             int64_t block_kv) {
+  TORCH_CHECK(q.dim() == 4 && k.dim() == 4, "expected (B, H, L, D) operands");
+  const int64_t H = q.size(1), Hkv = k.size(1);
+  TORCH_CHECK(Hkv > 0 && H % Hkv == 0, H, " query heads are not a multiple of ", Hkv, " key/value heads");
+  fa_b200_problem p{};
+  p.B = static_cast<int32_t>(q.size(0));
+  p.H = static_cast<int32_t>(H);
+  p.Lq = static_cast<int32_t>(q.size(2));
+  p.Lk = static_cast<int32_t>(k.size(2));
+  p.D = static_cast<int32_t>(q.size(3));
+  p.dtype = dtype_code(q);
+  p.causal = causal ? 1 : 0;
+  p.softmax_scale = static_cast<float>(scale);
+  p.block_q_hint = static_cast<int32_t>(block_q);
+  p.block_kv_hint = static_cast<int32_t>(block_kv);
+  p.q_pos0 = 0;
+  p.kv_pos0 = 0;
+  p.H_kv = Hkv == H ? 0 : static_cast<int32_t>(Hkv);
+  return p;
+}
+
+void check(int rc, const char *what) {
+  TORCH_CHECK(rc == 0, what, " failed (status ", rc, "): ", fa_b200_last_error());
+}
+
+void run_fwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const Tensor &v, const Tensor &o,
+             const Tensor &lse) {
+  const c10::cuda::CUDAGuard guard(q.device());
+  const fa_b200_tensor tq = desc(q), tk = desc(k), tv = desc(v), to = desc(o);
+  check(fa_b200_fwd(&p, &tq, &tk, &tv, &to, lse.data_ptr<float>(),
+                    c10::cuda::getCurrentCUDAStream(q.device().index()).stream()),
+        "fa_b200_fwd");
+}
+
+void run_bwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const Tensor &v, const Tensor &o,
+             const Tensor &dout, const Tensor &lse, const Tensor &dq, const Tensor &dk, const Tensor &dv) {
+  const c10::cuda::CUDAGuard guard(q.device());
+  const int64_t ws_bytes = static_cast<int64_t>(fa_b200_bwd_workspace_bytes(&p));
+  const Tensor ws = at::empty({ws_bytes}, q.options().dtype(at::kByte));
+  const fa_b200_tensor tq = desc(q), tk = desc(k), tv = desc(v), to = desc(o), tdo = desc(dout);
+  const fa_b200_tensor tdq = desc(dq), tdk = desc(dk), tdv = desc(dv);
+  check(fa_b200_bwd(&p, &tq, &tk, &tv, &to, &tdo, lse.data_ptr<float>(), &tdq, &tdk, &tdv, ws.data_ptr(),
+                    static_cast<size_t>(ws_bytes), c10::cuda::getCurrentCUDAStream(q.device().index()).stream()),
+        "fa_b200_bwd");
+}
+
+// ------------------------------------------------------------------ separate q, k, v (SDPA path)
+std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, const Tensor &v_, double scale,
+                                         bool causal, int64_t block_q, int64_t block_kv) {
+  require_cuda({&q_, &k_, &v_});
+  const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_);
+  Tensor out = at::empty_like(q);  // keeps q's (possibly (B,L,H,D)-transposed) dense layout
+  if (out.stride(-1) != 1) out = at::empty(q.sizes(), q.options());
+  const Tensor lse = at::empty({q.size(0), q.size(1), q.size(2)}, q.options().dtype(at::kFloat));
+  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out, lse);
+  return {out, lse};
+}
+
+std::tuple<Tensor, Tensor, Tensor> attention_bwd(const Tensor &dout_, const Tensor &q_, const Tensor &k_,
+                                                 const Tensor &v_, const Tensor &out_, const Tensor &lse,
+                                                 double scale, bool causal, int64_t block_q, int64_t block_kv) {
+  require_cuda({&dout_, &q_, &k_, &v_, &out_, &lse});
+  const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_), out = as_bhld(out_), dout = as_bhld(dout_);
+  const Tensor dq = at::empty_like(q), dk = at::empty_like(k), dv = at::empty_like(v);
+  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out, dout, lse, dq, dk, dv);
+  return {dq, dk, dv};
+}
+
+// ------------------------------------------------------------------ packed qkv (reference API)
+// (3,G,L,D) is B=1, H=G with q/k/v = base + {0,1,2}*G*L*D: zero-copy views.
+std::tuple<Tensor, Tensor> qkv_packed_fwd(const Tensor &qkv_, double scale, bool causal, int64_t block_q,
+                                          int64_t block_kv) {
+  require_cuda({&qkv_});
+  TORCH_CHECK(qkv_.dim() == 4 && qkv_.size(0) == 3, "expected a packed (3, G, L, D) tensor");
+  const Tensor qkv = qkv_.contiguous();
+  const Tensor q = qkv[0].unsqueeze(0), k = qkv[1].unsqueeze(0), v = qkv[2].unsqueeze(0);
+  const Tensor out = at::empty({qkv.size(1), qkv.size(2), qkv.size(3)}, qkv.options());
+  const Tensor lse = at::empty({qkv.size(1), qkv.size(2)}, qkv.options().dtype(at::kFloat));
+  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out.unsqueeze(0), lse);
+  return {out, lse};
+}
+
+Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out_, const Tensor &lse,
+                      double scale, bool causal, int64_t block_q, int64_t block_kv) {
+  require_cuda({&dout_, &qkv_, &out_, &lse});
+  const Tensor qkv = qkv_.contiguous(), dout = dout_.contiguous(), out = out_.contiguous();
+  const Tensor q = qkv[0].unsqueeze(0), k = qkv[1].unsqueeze(0), v = qkv[2].unsqueeze(0);
+  const Tensor dqkv = at::empty_like(qkv);  // gradients land directly in the packed buffer
+  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out.unsqueeze(0), dout.unsqueeze(0), lse,
+          dqkv[0].unsqueeze(0), dqkv[1].unsqueeze(0), dqkv[2].unsqueeze(0));
+  return dqkv;
+}
+
+// ------------------------------------------------------------------ autograd
+using torch::autograd::AutogradContext;
+using torch::autograd::variable_list;
+
+template <typename Sig>
+auto typed_op(const char *name) {
+  return c10::Dispatcher::singleton().findSchemaOrThrow(name, "").typed<Sig>();
+}
+
+struct AttentionFn : public torch::autograd::Function<AttentionFn> {
+  static variable_list forward(AutogradContext *ctx, const Tensor &q, const Tensor &k, const Tensor &v,
+                               double scale, bool causal, int64_t block_q, int64_t block_kv) {
+    at::AutoDispatchBelowADInplaceOrView below;
+    static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, const Tensor &, const Tensor &, double,
+                                                         bool, int64_t, int64_t)>("flash_attention_ipu::attention_fwd");
+    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv);
+    ctx->save_for_backward({q, k, v, out, lse});
+    ctx->saved_data["scale"] = scale;
+    ctx->saved_data["causal"] = causal;
+    ctx->saved_data["block_q"] = block_q;
+    ctx->saved_data["block_kv"] = block_kv;
+    ctx->mark_non_differentiable({lse});
+    return {out, lse};
+  }
+  static variable_list backward(AutogradContext *ctx, variable_list grads) {
+    static auto op = typed_op<std::tuple<Tensor, Tensor, Tensor>(
+        const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
+        int64_t, int64_t)>("flash_attention_ipu::attention_bwd");
+    const auto saved = ctx->get_saved_variables();
+    const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[3]);
+    auto [dq, dk, dv] = op.call(dout, saved[0], saved[1], saved[2], saved[3], saved[4],
+                                ctx->saved_data["scale"].toDouble(), ctx->saved_data["causal"].toBool(),
+                                ctx->saved_data["block_q"].toInt(), ctx->saved_data["block_kv"].toInt());
+    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor()};
+  }
+};
+
+struct PackedFn : public torch::autograd::Function<PackedFn> {
+  static variable_list forward(AutogradContext *ctx, const Tensor &qkv, double scale, bool causal,
+                               int64_t block_q, int64_t block_kv) {
+    at::AutoDispatchBelowADInplaceOrView below;
+    static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, double, bool, int64_t, int64_t)>(
+        "flash_attention_ipu::qkv_packed_fwd");
+    auto [out, lse] = op.call(qkv, scale, causal, block_q, block_kv);
+    ctx->save_for_backward({qkv, out, lse});
+    ctx->saved_data["scale"] = scale;
+    ctx->saved_data["causal"] = causal;
+    ctx->saved_data["block_q"] = block_q;
+    ctx->saved_data["block_kv"] = block_kv;
+    ctx->mark_non_differentiable({lse});
+    return {out, lse};
+  }
+  static variable_list backward(AutogradContext *ctx, variable_list grads) {
+    static auto op = typed_op<Tensor(const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
+                                     int64_t, int64_t)>("flash_attention_ipu::qkv_packed_bwd");
+    const auto saved = ctx->get_saved_variables();
+    const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[1]);
+    const Tensor dqkv = op.call(dout, saved[0], saved[1], saved[2], ctx->saved_data["scale"].toDouble(),
+                                ctx->saved_data["causal"].toBool(), ctx->saved_data["block_q"].toInt(),
+                                ctx->saved_data["block_kv"].toInt());
+    return {dqkv, Tensor(), Tensor(), Tensor(), Tensor()};
+  }
+};
+
+std::tuple<Tensor, Tensor> attention_fwd_autograd(const Tensor &q, const Tensor &k, const Tensor &v, double scale,
+                                                  bool causal, int64_t block_q, int64_t block_kv) {
+  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv);
+  return {r[0], r[1]};
+}
+
+std::tuple<Tensor, Tensor> qkv_packed_fwd_autograd(const Tensor &qkv, double scale, bool causal, int64_t block_q,
+                                                   int64_t block_kv) {
+  auto r = PackedFn::apply(qkv, scale, causal, block_q, block_kv);
+  return {r[0], r[1]};
+}
+
+}  // namespace
+
+TORCH_LIBRARY(flash_attention_ipu, m) {
+  m.def("attention_fwd(Tensor q, Tensor k, Tensor v, float softmax_scale, bool causal, int block_q, "
+        "int block_kv) -> (Tensor, Tensor)");
+  m.def("attention_bwd(Tensor dout, Tensor q, Tensor k, Tensor v, Tensor out, Tensor lse, float softmax_scale, "
+        "bool causal, int block_q, int block_kv) -> (Tensor, Tensor, Tensor)");
+  m.def("qkv_packed_fwd(Tensor qkv, float softmax_scale, bool causal, int block_q, int block_kv) -> "
+        "(Tensor, Tensor)");
+  m.def("qkv_packed_bwd(Tensor dout, Tensor qkv, Tensor out, Tensor lse, float softmax_scale, bool causal, "
+        "int block_q, int block_kv) -> Tensor");
+}
+
+// The implementations refuse non-CUDA tensors themselves ("there is no CPU path"), so they are
+// registered for every backend: a CPU tensor gets that message, not a dispatcher error.
+TORCH_LIBRARY_IMPL(flash_attention_ipu, CompositeExplicitAutograd, m) {
+  m.impl("attention_fwd", &attention_fwd);
+  m.impl("attention_bwd", &attention_bwd);
+  m.impl("qkv_packed_fwd", &qkv_packed_fwd);
+  m.impl("qkv_packed_bwd", &qkv_packed_bwd);
+}
+
+TORCH_LIBRARY_IMPL(flash_attention_ipu, Autograd, m) {
+  m.impl("attention_fwd", &attention_fwd_autograd);
+  m.impl("qkv_packed_fwd", &qkv_packed_fwd_autograd);
+}

@@ -104,3 +104,16 @@ def test_chunk_heuristic_matches_reference_formula():
     for L in (64, 256, 512, 1024, 4096, 8192, 131072):
         for D in (64, 128):
             assert _chunk_heuristic(L, D) == heuristic_chunks(L, D)
+
+
+def test_ops_library_registers_the_four_ops():
+    """csrc/torch_ops.cpp: loading build/libfa_torch_ops.so defines the ops (no Python fallback)."""
+    from flash_attention_ipu_b200._impl import ops
+    assert ops.ops_library_path.endswith("libfa_torch_ops.so")
+    for name in ("attention_fwd", "attention_bwd", "qkv_packed_fwd", "qkv_packed_bwd"):
+        assert hasattr(torch.ops.flash_attention_ipu, name)
+    x = torch.randn(1, 2, 8, 8)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ops.attention_fwd(x, x, x, 1.0, True, 0, 0)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ops.qkv_packed_bwd(x[0], torch.randn(3, 2, 8, 8), x[0], torch.randn(2, 8), 1.0, True, 0, 0)
