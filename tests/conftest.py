@@ -13,8 +13,20 @@ GOLDEN = ROOT / "tests" / "golden"
 SEED = 1123581321  # the reference tests' seed (tests/python/test_flash_attention_qkv_packed.py:59)
 
 
+_LIBS = ("libflash_attention.so", "libfa_torch_ops.so", "liboracle.so")
+
+
+def _ensure_built():
+    """The package refuses to import without its native libraries (no fallback), so a fresh
+    checkout is built once here (nvcc / g++ cross-compile without a GPU)."""
+    missing = [name for name in _LIBS if not (ROOT / "build" / name).exists()]
+    if missing:
+        subprocess.check_call(["make", "-s"] + [f"build/{name}" for name in missing], cwd=ROOT)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    _ensure_built()
 
 
 def pytest_collection_modifyitems(config, items):
@@ -29,8 +41,7 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def built():
     """Make sure the native libraries exist (nvcc cross-compiles without a GPU)."""
-    if not (ROOT / "build" / "libflash_attention.so").exists() or not (ROOT / "build" / "liboracle.so").exists():
-        subprocess.check_call(["make", "-s", "build/libflash_attention.so", "build/liboracle.so"], cwd=ROOT)
+    _ensure_built()
     return ROOT / "build"
 
 
