@@ -22,7 +22,8 @@
 //     is the only way to the fp32 peak.  NT packs along the contraction (even/odd partial sums,
 //     the float4 operand loads are already register pairs); NN packs along the output columns
 //     with the P value duplicated into both halves.
-// Exponentials are exp2 with log2(e) folded into the stationary operand's scale.
+// Exponentials are exp2; softmax_scale * log2(e) is folded into the FFMA that forms the exponent, so
+// every operand tile is staged unscaled (and, for fp32 inputs, by cp.async).
 #pragma once
 #include "fa_generic.cuh"
 #include "sm100_ptx.cuh"
@@ -217,7 +218,7 @@ template <int DP> constexpr size_t t_fwd_smem() { return (3 * kTB * (DP + 4) + k
 template <int DP> constexpr size_t t_bwd_smem() { return (4 * kTB * (DP + 4) + kTB * kTLdp + 2 * kTB) * sizeof(float); }
 
 // ------------------------------------------------------------------ forward
-// grid (query tiles, B*H).  Q tile stationary (scaled by softmax_scale * log2 e), K/V streamed.
+// grid (query tiles, B*H).  Q tile stationary, K/V streamed.
 template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
 fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o, float *lse,
@@ -228,7 +229,10 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   const int g = blockIdx.y, b = g / p.H, h = g % p.H;
   const int m0 = (gridDim.x - 1 - blockIdx.x) * kTB;  // longest (latest) causal rows first
-  t_load_tile<T, DP>(Qs, q.row(b, h, 0), q.sl, m0, p.Lq, p.D, p.scale * kTLog2e);
+  // Q goes to shared memory unscaled (same asynchronous copy as the streamed tiles, in flight
+  // together with K(0)); softmax_scale * log2(e) is folded into the exponent's FFMA instead.
+  t_stream_tile<T, DP, kAsync>(Qs, q.row(b, h, 0), q.sl, m0, p.Lq, p.D);
+  const float c2 = p.scale * kTLog2e;
   int hi = p.Lk;
   if (p.causal) hi = min(hi, m0 + kTB + p.shift);  // last row of the tile sees keys < m0+63+shift+1
 
@@ -271,11 +275,12 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
       const float mx = t_max16(fmaxf(fmaxf(s[i][0], s[i][1]), fmaxf(s[i][2], s[i][3])));
       const float m_new = fmaxf(m[i], mx);
       const float m_use = m_new == -INFINITY ? 0.f : m_new;  // a row with nothing visible yet
-      const float corr = t_exp2(m[i] - m_use);
+      const float corr = t_exp2((m[i] - m_use) * c2);
+      const float nm = -m_use * c2;
       float part = 0.f;
       #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float e = t_exp2(s[i][j] - m_use);
+        const float e = t_exp2(fmaf(s[i][j], c2, nm));
         part += e;
         Ps[(ty + 8 * i) * kTLdp + tx + 16 * j] = e;
       }
@@ -289,6 +294,7 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
     __syncthreads();
     t_gemm_nn<DP>(Ps, Vs, ty, tx, acc);
   }
+  t_stream_wait<kAsync, 0>();  // (a tile with no visible key still issued its Q copy)
   float inv[8];
   #pragma unroll
   for (int i = 0; i < 8; ++i) {
@@ -296,13 +302,13 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
     inv[i] = lt > 0.f ? 1.f / lt : 0.f;
     const int r = m0 + ty + 8 * i;
     if (tx == 0 && r < p.Lq)
-      lse[static_cast<int64_t>(g) * p.Lq + r] = lt > 0.f ? (m[i] + log2f(lt)) * kTLn2 : -INFINITY;
+      lse[static_cast<int64_t>(g) * p.Lq + r] = lt > 0.f ? (m[i] * c2 + log2f(lt)) * kTLn2 : -INFINITY;
   }
   t_store_rows<DP, T>(o.row(b, h, 0), o.sl, m0, p.Lq, p.D, ty, tx, acc, inv);
 }
 
 // ------------------------------------------------------------------ backward: dQ
-// grid (query tiles, B*H).  Q (scaled) and dO stationary, K/V streamed.
+// grid (query tiles, B*H).  Q and dO stationary, K/V streamed.
 // P = exp(S - LSE) (:457-459); dP = dO V^T (:465); dS = P (dP - delta) (:466-467); dQ += dS K (:470)
 template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
@@ -314,10 +320,17 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   const int g = blockIdx.y, b = g / p.H, h = g % p.H;
   const int m0 = (gridDim.x - 1 - blockIdx.x) * kTB;
-  t_load_tile<T, DP>(Qs, q.row(b, h, 0), q.sl, m0, p.Lq, p.D, p.scale * kTLog2e);
-  t_load_tile<T, DP>(Ds, dout.row(b, h, 0), dout.sl, m0, p.Lq, p.D, 1.f);
   int hi = p.Lk;
   if (p.causal) hi = min(hi, m0 + kTB + p.shift);
+  const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
+  // Prologue copies, all in flight at once: Q and dO (stationary, unscaled -- softmax_scale *
+  // log2(e) is folded into the exponent's FFMA), the O tile (parked in the K buffer, only needed
+  // for delta) and V(0).
+  t_stream_tile<T, DP, kAsync>(Qs, q.row(b, h, 0), q.sl, m0, p.Lq, p.D);
+  t_stream_tile<T, DP, kAsync>(Ds, dout.row(b, h, 0), dout.sl, m0, p.Lq, p.D);
+  t_stream_tile<T, DP, kAsync>(Ks, o.row(b, h, 0), o.sl, m0, p.Lq, p.D);
+  if (hi > 0) t_stream_tile<T, DP, kAsync>(Vs, vslab, v.sl, 0, p.Lk, p.D);
+  const float c2 = p.scale * kTLog2e;
 
   uint64_t acc[8][NC];
   float lse2[8], dl[8];
@@ -325,34 +338,35 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
   for (int i = 0; i < 8; ++i) {
     const int r = m0 + ty + 8 * i;
     float ls = INFINITY;  // exp2(s - inf) = 0: rows that saw no key, rows past the end
-    // delta = rowsum(O o dO) (:374-377) is computed here, 16 lanes per row, and written out for
-    // the dK/dV kernel that follows on the stream -- no separate pass over O and dO
-    float part = 0.f;
     if (r < p.Lq) {
       const float x = lse[static_cast<int64_t>(g) * p.Lq + r];
       if (x > -INFINITY) ls = x * kTLog2e;
-      const T *orow = o.row(b, h, r), *drow = dout.row(b, h, r);
-      #pragma unroll
-      for (int jj = 0; jj < DP / 64; ++jj) {
-        #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int d = tx * 4 + 64 * jj + e;
-          if (d < p.D) part = fmaf(to_f32(orow[d]), to_f32(drow[d]), part);
-        }
-      }
     }
-    dl[i] = t_sum16(part);
-    if (tx == 0 && r < p.Lq) delta[static_cast<int64_t>(g) * p.Lq + r] = dl[i];
     lse2[i] = ls;
     #pragma unroll
     for (int c = 0; c < NC; ++c) acc[i][c] = 0ull;
   }
-  const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
+  t_stream_wait<kAsync, 0>();
+  __syncthreads();
+  // delta = rowsum(O o dO) (:374-377), 16 lanes per row from the two staged tiles; written out for
+  // the dK/dV kernel that follows on the stream -- no separate pass over O and dO
+  #pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = m0 + ty + 8 * i;
+    float part = 0.f;
+    #pragma unroll
+    for (int jj = 0; jj < DP / 64; ++jj) {
+      const float4 ov = *reinterpret_cast<const float4 *>(Ks + (ty + 8 * i) * LD + tx * 4 + 64 * jj);
+      const float4 dv4 = *reinterpret_cast<const float4 *>(Ds + (ty + 8 * i) * LD + tx * 4 + 64 * jj);
+      part = fmaf(ov.x, dv4.x, fmaf(ov.y, dv4.y, fmaf(ov.z, dv4.z, fmaf(ov.w, dv4.w, part))));
+    }
+    dl[i] = t_sum16(part);
+    if (tx == 0 && r < p.Lq) delta[static_cast<int64_t>(g) * p.Lq + r] = dl[i];
+  }
   // V(n) is fetched while Q K(n-1)^T and dS K(n-1) run, K(n) while dO V(n)^T runs.
-  if (hi > 0) t_stream_tile<T, DP, kAsync>(Vs, vslab, v.sl, 0, p.Lk, p.D);
   for (int n0 = 0; n0 < hi; n0 += kTB) {
     t_stream_wait<kAsync, 0>();
-    __syncthreads();  // V(n0) has landed; everyone is done with the previous K tile
+    __syncthreads();  // V(n0) has landed; everyone is done with the previous K tile (or the O tile)
     t_stream_tile<T, DP, kAsync>(Ks, kslab, k.sl, n0, p.Lk, p.D);
     float s[8][4], dp[8][4];
     #pragma unroll
@@ -372,7 +386,7 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
       for (int j = 0; j < 4; ++j) {
         const int c = n0 + tx + 16 * j;
         const bool hidden = c >= p.Lk || (p.causal && c > r + p.shift);
-        const float pe = hidden ? 0.f : t_exp2(s[i][j] - lse2[i]);
+        const float pe = hidden ? 0.f : t_exp2(fmaf(s[i][j], c2, -lse2[i]));
         Ps[(ty + 8 * i) * kTLdp + tx + 16 * j] = pe * (dp[i][j] - dl[i]);
       }
     }
@@ -386,7 +400,7 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
 }
 
 // ------------------------------------------------------------------ backward: dK, dV
-// grid (key tiles, B*H).  K (scaled) and V stationary, Q/dO streamed; the score tile is held
+// grid (key tiles, B*H).  K and V stationary, Q/dO streamed; the score tile is held
 // transposed (rows = keys) so that dV += P^T dO (:462) and dK += dS^T Q (:472) are NN products.
 template <typename T, int DP, bool kAsync>
 __global__ void __launch_bounds__(kTThreads)
@@ -400,8 +414,10 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
   const int g = blockIdx.y, b = g / p.H, h = g % p.H;
   const int n0 = blockIdx.x * kTB;  // earliest keys have the most causal work
-  t_load_tile<T, DP>(Ks, k.row(b, h, 0), k.sl, n0, p.Lk, p.D, p.scale * kTLog2e);
-  t_load_tile<T, DP>(Vs, v.row(b, h, 0), v.sl, n0, p.Lk, p.D, 1.f);
+  // stationary K, V: unscaled, copied asynchronously together with the first dO tile
+  t_stream_tile<T, DP, kAsync>(Ks, k.row(b, h, 0), k.sl, n0, p.Lk, p.D);
+  t_stream_tile<T, DP, kAsync>(Vs, v.row(b, h, 0), v.sl, n0, p.Lk, p.D);
+  const float c2 = p.scale * kTLog2e;
   int m_start = 0;  // first query tile with a row that sees key n0+63... or any key of the tile
   if (p.causal) m_start = (max(0, n0 - p.shift) / kTB) * kTB;
 
@@ -446,7 +462,7 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
       for (int i = 0; i < 8; ++i) {
         const int c = n0 + ty + 8 * i;
         const bool hidden = c >= p.Lk || r >= p.Lq || (p.causal && c > r + p.shift);
-        const float pe = hidden ? 0.f : t_exp2(s[i][j] - ls);
+        const float pe = hidden ? 0.f : t_exp2(fmaf(s[i][j], c2, -ls));
         s[i][j] = pe;
         dp[i][j] = pe * (dp[i][j] - dl);
       }
@@ -468,6 +484,7 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
     __syncwarp();
     t_gemm_nn<DP>(Ps, Qs, ty, tx, acck);
   }
+  t_stream_wait<kAsync, 0>();  // (a key tile no query row sees still issued its K, V copies)
   float mulk[8], mulv[8];
   #pragma unroll
   for (int i = 0; i < 8; ++i) { mulk[i] = p.scale; mulv[i] = 1.f; }
