@@ -9,7 +9,7 @@ NVFLAGS ?= -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-Wall -Xptxas -v
 CSRC    := flash_attention_ipu_b200/csrc
 HDRS    := $(wildcard $(CSRC)/*.cuh) include/fa_b200.h
 
-all: $(OUT)/libflash_attention.so $(OUT)/libfa_torch_ops.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe $(OUT)/umma_rate $(OUT)/exp_rate
+all: $(OUT)/libflash_attention.so $(OUT)/libfa_torch_ops.so $(OUT)/liboracle.so $(OUT)/tests $(OUT)/umma_probe $(OUT)/umma2_probe $(OUT)/umma_rate $(OUT)/exp_rate
 
 $(OUT)/libflash_attention.so: $(CSRC)/fa_api.cu $(HDRS)
 	@mkdir -p $(OUT)
@@ -37,6 +37,11 @@ $(OUT)/tests: tests/cuda/test_flash_attention.cu oracle/vanilla_attention.c $(OU
 	    -L$(OUT) -lflash_attention -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 $(OUT)/umma_probe: tests/cuda/umma_probe.cu $(CSRC)/sm100_ptx.cuh
+	@mkdir -p $(OUT)
+	$(NVCC) -std=c++17 -O2 -lineinfo $(ARCH) -o $@ $<
+
+# CTA-pair (cta_group::2) probes: accumulator layouts, operand splits, issue rates
+$(OUT)/umma2_probe: tests/cuda/umma2_probe.cu $(CSRC)/sm100_ptx.cuh
 	@mkdir -p $(OUT)
 	$(NVCC) -std=c++17 -O2 -lineinfo $(ARCH) -o $@ $<
 

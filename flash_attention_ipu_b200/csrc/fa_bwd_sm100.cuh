@@ -224,6 +224,55 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       long long tr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       const long long t_loop = clock64();
 #endif
+#ifdef FA_BWD_DK_TS
+      // Variant: dS^T is ALSO written to TMEM (packed, over the dP^T columns its warpgroup has
+      // already read) and dK += dS^T Q takes it from there (TS form: no shared-memory A reads).
+      // dQ aliases dP^T, so dK must be issued before dQ; the order becomes
+      //   dV(it) dP(it) S(it+1) dK(it) dQ(it)
+      // and dV(it+1) is what runs while the drain empties dQ(it).
+      for (int it = 0; it < n; ++it) {
+        const uint32_t q_stage = (it & 1) * kTile16;
+        FA_BT_WAIT(2, mbar_wait(p_full, it & 1));
+        FA_BT_WAIT(0, mbar_wait(do_full, it & 1));
+        tc_fence_after();
+        if (leader) {
+          #pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ts2(tDV, tS + (k < 4 ? 8 * k : 64 + 8 * (k - 4)), do_mn + k * (2048 >> 4), hi, idesc_dv,
+                     (it > 0 || k > 0));
+        }
+        if (it > 0) FA_BT_WAIT(1, mbar_wait(dq_empty, (it - 1) & 1));
+        tc_fence_after();
+        if (leader) {
+          issue_kk(tDP, v_kmaj, do_kmaj);
+          umma_commit(dp_full);
+          umma_commit(do_empty);
+        }
+        if (it + 1 < n) {
+          FA_BT_WAIT(3, mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1));
+          tc_fence_after();
+          if (leader) {
+            issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16);
+            umma_commit(s_full);
+          }
+        }
+        FA_BT_WAIT(4, mbar_wait(ds_full, it & 1));
+        tc_fence_after();
+        if (leader) {
+          #pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ts2(tDK, tDP + (k < 4 ? 8 * k : 64 + 8 * (k - 4)), q_mn + q_stage + k * (2048 >> 4), hi,
+                     idesc_dv, (it > 0 || k > 0));
+          umma_commit(&q_empty[it & 1]);
+          #pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ss2(tDP, ds_mn + k * (2048 >> 4), hi, k_mn + k * (2048 >> 4), hi, idesc_dq, k > 0);
+          umma_commit(dq_full);
+        }
+        __syncwarp();
+      }
+      (void)ds_kmaj;
+#else
       for (int it = 0; it < n; ++it) {
         const uint32_t q_stage = (it & 1) * kTile16;
         // dP^T(it) = V dO^T   (overwrites dQ(it-1): the drain must have emptied it)
@@ -271,6 +320,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         __syncwarp();
       }
+#endif
       if (leader) umma_commit(dkv_full);
 #ifdef FA_BWD_TRACE
       if (blockIdx.x == 0 && lane == 0) {
@@ -431,6 +481,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
           }
         }
+#ifdef FA_BWD_DK_TS
+        tmem_st16(tDP + hf * 16, w);  // the TMEM copy (A operand of dK): columns this thread has already read
+#endif
         #pragma unroll
         for (int c8 = 0; c8 < 4; ++c8) {  // 8 columns -> one 16-byte chunk
           const int chunk = (hf * 4 + c8) ^ (row & 7);
@@ -439,6 +492,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
       }
       fence_proxy_async_smem();
+#ifdef FA_BWD_DK_TS
+      tmem_st_wait();
+#endif
       tc_fence_before();
       mbar_arrive_warp(ds_full);
     }

@@ -1,0 +1,377 @@
+// umma2_probe.cu -- CTA-pair (cta_group::2) probes: the building blocks a 2-CTA forward / backward
+// would rely on, checked before any kernel is built on them.
+// Integer-valued bf16 inputs make every product exact, so a mismatch is a layout / descriptor /
+// protocol error, never rounding.  Each mode first runs with CODED operands (D[m][n] = m + 256 n)
+// to DISCOVER where the pair's accumulator rows live in each CTA's TMEM, prints that map, then
+// runs random operands and verifies them through the discovered map.
+//   umma2_probe <mode>
+//   0: M=256  D_c[128x128] = A_c[128 x K=128] * B[128 x K]^T   SS, A K-major, B K-major, B split by N
+//                                                              (S = Q K^T: each CTA loads 64 keys)
+//   1: M=256  D_c = P_c[128 x K=128] * V[K=128 x 128]          TS, A in TMEM, B MN-major split by N
+//                                                              (O += P V: each CTA loads 64 columns of V)
+//   2: M=128  D[128x128] = A[128 x K=128] * B[128 x K]^T       SS K/K, 64 rows of D per CTA
+//   3: M=128  D = At[K=128 x 128]^T * Bt[K x 128]              SS, A MN-major (64 columns of At per
+//                                                              CTA), B MN-major split by N (dQ = dS K)
+//   10+: issue-rate modes, all SMs busy: clk per tcgen05.mma with `traffic` 16-byte shared-memory
+//        stores per thread per loop turn from 4 bystander warps (models TMA writes / drain staging)
+//        umma2_probe 10 <traffic>   cta_group::1 SS 128x128x16   (today's kernels)
+//        umma2_probe 11 <traffic>   cta_group::2 SS 256x128x16   (B split over the pair)
+//        umma2_probe 12 <traffic>   cta_group::2 SS 128x128x16   (64 rows per CTA)
+//        umma2_probe 13 <traffic>   cta_group::2 TS 256x128x16
+//        umma2_probe 14 <traffic>   cta_group::1 TS 128x128x16
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <vector>
+#include <cuda_bf16.h>
+#include "../../flash_attention_ipu_b200/csrc/sm100_ptx.cuh"
+
+using namespace fa;
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(2); } } while (0)
+
+// ------------------------------------------------------------------ cta_group::2 wrappers
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc2(uint32_t *smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "n"(kCols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+__device__ __forceinline__ void umma2_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma2_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+               ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in every CTA of `mask`
+__device__ __forceinline__ void umma2_commit_mc(uint64_t *bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// bf16 [rows][cols] row-major, box = 64 columns x 128 rows, 128-byte swizzle, OOB rows read as zero
+static CUtensorMap make_map(void *ptr, int rows, int cols) {
+  void *sym = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q));
+  CUtensorMap m;
+  cuuint64_t dims[4] = {(cuuint64_t)cols, (cuuint64_t)rows, 1, 1};
+  cuuint64_t strides[3] = {(cuuint64_t)cols * 2, (cuuint64_t)rows * cols * 2, (cuuint64_t)rows * cols * 2};
+  cuuint32_t box[4] = {64, 128, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = ((EncodeTiledFn)sym)(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { printf("encode failed %d\n", (int)r); exit(2); }
+  return m;
+}
+
+// ------------------------------------------------------------------ layout / correctness kernel
+// smem per CTA: A panels at 0 / 16 KB, B panels at 32 / 48 KB (each [128 rows][64 bf16], SW128)
+// d_out: [2 CTAs][128 lanes][128 columns] fp32 = the raw TMEM image of the accumulator region
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+probe2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+              const __nv_bfloat16 *a_gmem, float *d_out, int mode) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t *bar_ld = (uint64_t *)(smem + 65536);
+  uint64_t *bar_mma = bar_ld + 1;
+  uint32_t *tptr = (uint32_t *)(bar_ld + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  if (threadIdx.x == 0) { mbar_init(bar_ld, 1); mbar_init(bar_mma, 1); fence_barrier_init(); }
+  if (warp == 1) tmem_alloc2<256>(tptr);
+  tc_fence_before(); __syncthreads(); cluster_sync_all(); tc_fence_after();
+  const uint32_t tb = *tptr;
+  const uint32_t tD = tb, tP = tb + 128;
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(bar_ld, mode == 1 ? 16384 : (mode == 3 ? 32768 : 65536));
+    if (mode == 0) {         // A rows [128 rank, +128), B rows [64 rank, +64) (box reads 128; the rest is unused)
+      for (int p = 0; p < 2; ++p) {
+        tma_load_4d(&tmA, bar_ld, smem + p * 16384, p * 64, 128 * rank, 0, 0);
+        tma_load_4d(&tmB, bar_ld, smem + 32768 + p * 16384, p * 64, 64 * rank, 0, 0);
+      }
+    } else if (mode == 1) {  // B = V[:, 64 rank .. +64): one panel, all 128 keys
+      tma_load_4d(&tmB, bar_ld, smem + 32768, 64 * rank, 0, 0, 0);
+    } else if (mode == 2) {  // A rows [64 rank, +64), B rows [64 rank, +64)
+      for (int p = 0; p < 2; ++p) {
+        tma_load_4d(&tmA, bar_ld, smem + p * 16384, p * 64, 64 * rank, 0, 0);
+        tma_load_4d(&tmB, bar_ld, smem + 32768 + p * 16384, p * 64, 64 * rank, 0, 0);
+      }
+    } else {                 // mode 3: At[:, 64 rank .. +64) and Bt[:, 64 rank .. +64): one panel each
+      tma_load_4d(&tmA, bar_ld, smem, 64 * rank, 0, 0, 0);
+      tma_load_4d(&tmB, bar_ld, smem + 32768, 64 * rank, 0, 0, 0);
+    }
+  }
+  {  // sentinel over the accumulator region so untouched cells are recognisable
+    uint32_t w[32];
+    for (int e = 0; e < 32; ++e) w[e] = 0x7fc00000u;
+    for (int c = 0; c < 4; ++c) tmem_st32(tD + ((uint32_t)(warp * 32) << 16) + c * 32, w);
+    tmem_st_wait();
+  }
+  if (mode == 1) {  // P_c = A rows [128 rank, +128) -> TMEM, two bf16 per 32-bit column
+    const int row = 128 * rank + warp * 32 + lane;
+    const uint32_t *src = (const uint32_t *)(a_gmem + row * 128);
+    for (int c = 0; c < 4; ++c) {
+      uint32_t w[16];
+      for (int e = 0; e < 16; ++e) w[e] = src[c * 16 + e];
+      tmem_st16(tP + ((uint32_t)(warp * 32) << 16) + c * 16, w);
+    }
+    tmem_st_wait();
+  }
+  mbar_wait(bar_ld, 0);
+  tc_fence_before(); __syncthreads(); cluster_sync_all(); tc_fence_after();
+  if (rank == 0 && threadIdx.x == 0) {
+    const uint32_t a_addr = smem_u32(smem), b_addr = smem_u32(smem + 32768);
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t koff = (k / 4) * 16384 + (k % 4) * 32;  // K-major: 16 elements = 32 bytes, panel per 64
+      if (mode == 0)
+        umma2_ss(tD, make_smem_desc(a_addr + koff, 16, 1024), make_smem_desc(b_addr + koff, 16, 1024),
+                 make_idesc(256, 128, 1, 0, 0), k > 0);
+      else if (mode == 1)
+        umma2_ts(tD, tP + k * 8, make_smem_desc(b_addr + k * 2048, 16384, 1024),
+                 make_idesc(256, 128, 1, 0, 1), k > 0);
+      else if (mode == 2)
+        umma2_ss(tD, make_smem_desc(a_addr + koff, 16, 1024), make_smem_desc(b_addr + koff, 16, 1024),
+                 make_idesc(128, 128, 1, 0, 0), k > 0);
+      else
+        umma2_ss(tD, make_smem_desc(a_addr + k * 2048, 16384, 1024),
+                 make_smem_desc(b_addr + k * 2048, 16384, 1024), make_idesc(128, 128, 1, 1, 1), k > 0);
+    }
+    umma2_commit_mc(bar_mma, 3);
+  }
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+  for (int c = 0; c < 4; ++c) {
+    uint32_t r[32];
+    tmem_ld32(tD + ((uint32_t)(warp * 32) << 16) + c * 32, r);
+    tmem_ld_wait();
+    for (int e = 0; e < 32; ++e)
+      d_out[(rank * 128 + warp * 32 + lane) * 128 + c * 32 + e] = __uint_as_float(r[e]);
+  }
+  tc_fence_before(); __syncthreads(); cluster_sync_all();
+  if (warp == 1) tmem_dealloc2<256>(tb);
+}
+
+// ------------------------------------------------------------------ issue-rate kernel
+// warp 0: issuer (leader CTA only when kCg == 2); warps 1-4: shared-memory store traffic.
+template <int kCg, int kM, bool kTs>
+__global__ void __launch_bounds__(192, 1)
+rate_kernel(int n_mma, int traffic, long long *clk_out, long long *bytes_out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t *bar = (uint64_t *)(smem + 98304);
+  uint32_t *tptr = (uint32_t *)(bar + 2);
+  volatile int *stop = (volatile int *)(bar + 4);
+  const int warp = threadIdx.x >> 5;
+  uint32_t rank = 0;
+  if (kCg == 2) rank = cluster_ctarank();
+  for (int i = threadIdx.x; i < 98304 / 4; i += blockDim.x) ((uint32_t *)smem)[i] = 0;
+  if (threadIdx.x == 0) { mbar_init(bar, 1); *stop = 0; fence_barrier_init(); }
+  if (warp == 0) { if (kCg == 2) tmem_alloc2<256>(tptr); else tmem_alloc<256>(tptr); }
+  fence_proxy_async_smem();
+  tc_fence_before(); __syncthreads();
+  if (kCg == 2) cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tb = *tptr;
+  if (warp == 0) {
+    if (rank == 0 && threadIdx.x == 0) {
+      const uint32_t a_addr = smem_u32(smem), b_addr = smem_u32(smem + 32768);
+      const uint32_t idesc = make_idesc(kM, 128, 1, 0, 0);
+      const long long t0 = clock64();
+      for (int i = 0; i < n_mma; ++i) {
+        const uint32_t koff = ((i >> 2) & 1) * 16384 + (i & 3) * 32;
+        const uint64_t da = make_smem_desc(a_addr + koff, 16, 1024), db = make_smem_desc(b_addr + koff, 16, 1024);
+        if (kCg == 2) {
+          if (kTs) umma2_ts(tb, tb + 128 + (i & 7) * 8, db, idesc, 1); else umma2_ss(tb, da, db, idesc, 1);
+        } else {
+          if (kTs) umma_ts(tb, tb + 128 + (i & 7) * 8, db, idesc, 1); else umma_ss(tb, da, db, idesc, 1);
+        }
+      }
+      if (kCg == 2) umma2_commit_mc(bar, 1); else umma_commit(bar);
+      mbar_wait(bar, 0);
+      const long long t1 = clock64();
+      clk_out[blockIdx.x] = t1 - t0;
+      *stop = 1;
+    }
+  } else if (warp <= 4) {
+    // store traffic into [64 KB, 96 KB); runs until the issuer is done (leader) or a fixed count (peer)
+    uint4 v = make_uint4(threadIdx.x, 1, 2, 3);
+    const uint32_t sbase = smem_u32(smem + 65536 + (threadIdx.x - 32) * 16);
+    long long n = 0;
+    if (traffic > 0) {
+      const long long t0 = clock64();
+      long long limit = (kCg == 2 && rank == 1) ? (long long)n_mma * 64 : (1ll << 62);
+      while (!*stop && (clock64() - t0) < limit) {
+        for (int j = 0; j < traffic; ++j) { asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sbase + ((j & 15) * 2048)), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); v.x += 1; }
+        n += traffic;
+      }
+      if (threadIdx.x == 32) bytes_out[blockIdx.x] = n * 16 * 128 * 1000 / (clock64() - t0 + 1);  // mB/clk
+    } else if (threadIdx.x == 32) bytes_out[blockIdx.x] = 0;
+  }
+  tc_fence_before(); __syncthreads();
+  if (kCg == 2) cluster_sync_all();
+  if (warp == 0) { if (kCg == 2) tmem_dealloc2<256>(tb); else tmem_dealloc<256>(tb); }
+}
+
+template <int kCg, int kM, bool kTs>
+static void run_rate(const char *name, int traffic) {
+  int dev = 0, sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = sms & ~1, n_mma = 8192;
+  long long *clk, *byt;
+  CK(cudaMalloc(&clk, grid * 8)); CK(cudaMalloc(&byt, grid * 8));
+  CK(cudaMemset(clk, 0, grid * 8)); CK(cudaMemset(byt, 0, grid * 8));
+  auto kern = rate_kernel<kCg, kM, kTs>;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 99 * 1024));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(192); cfg.dynamicSmemBytes = 99 * 1024;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = kCg; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  for (int rep = 0; rep < 2; ++rep) {
+    CK(cudaLaunchKernelEx(&cfg, kern, n_mma, traffic, clk, byt));
+    CK(cudaDeviceSynchronize());
+  }
+  std::vector<long long> hc(grid), hb(grid);
+  CK(cudaMemcpy(hc.data(), clk, grid * 8, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(hb.data(), byt, grid * 8, cudaMemcpyDeviceToHost));
+  double sum = 0, mx = 0, bsum = 0; int n = 0, nb = 0;
+  for (int i = 0; i < grid; ++i) {
+    if (hc[i] > 0) { sum += hc[i]; mx = fmax(mx, (double)hc[i]); ++n; }
+    if (hb[i] > 0) { bsum += hb[i] / 1000.0; ++nb; }
+  }
+  printf("rate %-28s traffic %3d: %7.2f clk/MMA mean, %7.2f max over %d issuers; store traffic %.1f B/clk/SM\n",
+         name, traffic, sum / n / n_mma, mx / n_mma, n, nb ? bsum / nb : 0.0);
+}
+
+// ------------------------------------------------------------------ host side of the layout modes
+struct Problem {
+  int M;                       // rows of D over the pair
+  std::vector<float> A, B;     // as stored in global memory (see fill)
+  std::vector<float> ref;      // [M][128]
+};
+
+// storage: modes 0,2: A [M][128] (row m, k), B [128][128] (row n, k)
+//          mode 1:    A [256][128] = P (row m, k), B [128][128] = V (row k, n)
+//          mode 3:    A [128][128] = At (row k, m), B [128][128] = Bt (row k, n)
+static Problem make_problem(int mode, bool coded) {
+  Problem p;
+  p.M = (mode <= 1) ? 256 : 128;
+  const int N = 128, K = 128;
+  const int a_rows = (mode == 3) ? K : p.M;
+  p.A.assign((size_t)a_rows * 128, 0.f); p.B.assign(128 * 128, 0.f); p.ref.assign((size_t)p.M * N, 0.f);
+  auto a_at = [&](int m, int k) -> float & { return mode == 3 ? p.A[k * 128 + m] : p.A[m * 128 + k]; };
+  auto b_at = [&](int n, int k) -> float & { return (mode == 1 || mode == 3) ? p.B[k * 128 + n] : p.B[n * 128 + k]; };
+  srand(11 + mode);
+  for (int m = 0; m < p.M; ++m)
+    for (int k = 0; k < K; ++k) a_at(m, k) = coded ? (k == 0 ? (float)m : (k == 1 ? 256.f : 0.f)) : (float)(rand() % 7 - 3);
+  for (int n = 0; n < N; ++n)
+    for (int k = 0; k < K; ++k) b_at(n, k) = coded ? (k == 0 ? 1.f : (k == 1 ? (float)n : 0.f)) : (float)(rand() % 5 - 2);
+  for (int m = 0; m < p.M; ++m)
+    for (int n = 0; n < N; ++n) {
+      float s = 0;
+      for (int k = 0; k < K; ++k) s += a_at(m, k) * b_at(n, k);
+      p.ref[m * N + n] = s;
+    }
+  return p;
+}
+
+static std::vector<float> run_layout(int mode, const Problem &p) {
+  const size_t na = p.A.size(), nb = p.B.size();
+  std::vector<__nv_bfloat16> A(na), B(nb);
+  for (size_t i = 0; i < na; ++i) A[i] = __float2bfloat16(p.A[i]);
+  for (size_t i = 0; i < nb; ++i) B[i] = __float2bfloat16(p.B[i]);
+  __nv_bfloat16 *dA, *dB; float *dD;
+  CK(cudaMalloc(&dA, na * 2)); CK(cudaMalloc(&dB, nb * 2)); CK(cudaMalloc(&dD, 2 * 128 * 128 * 4));
+  CK(cudaMemcpy(dA, A.data(), na * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dB, B.data(), nb * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemset(dD, 0xff, 2 * 128 * 128 * 4));
+  CUtensorMap tA = make_map(dA, (int)(na / 128), 128), tB = make_map(dB, 128, 128);
+  CK(cudaFuncSetAttribute(probe2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 66 * 1024));
+  probe2_kernel<<<2, 128, 66 * 1024>>>(tA, tB, dA, dD, mode);
+  CK(cudaDeviceSynchronize());
+  std::vector<float> h(2 * 128 * 128);
+  CK(cudaMemcpy(h.data(), dD, h.size() * 4, cudaMemcpyDeviceToHost));
+  cudaFree(dA); cudaFree(dB); cudaFree(dD);
+  return h;
+}
+
+int main(int argc, char **argv) {
+  const int mode = argc > 1 ? atoi(argv[1]) : 0;
+  const int traffic = argc > 2 ? atoi(argv[2]) : 0;
+  if (mode >= 10) {
+    if (mode == 10) run_rate<1, 128, false>("cg1 SS 128x128x16", traffic);
+    if (mode == 11) run_rate<2, 256, false>("cg2 SS 256x128x16", traffic);
+    if (mode == 12) run_rate<2, 128, false>("cg2 SS 128x128x16 (64/CTA)", traffic);
+    if (mode == 13) run_rate<2, 256, true>("cg2 TS 256x128x16", traffic);
+    if (mode == 14) run_rate<1, 128, true>("cg1 TS 128x128x16", traffic);
+    return 0;
+  }
+  // 1. coded run: where does D[m][n] land?
+  Problem pc = make_problem(mode, true);
+  std::vector<float> img = run_layout(mode, pc);
+  std::vector<int> map_m(2 * 128 * 128, -1), map_n(2 * 128 * 128, -1);
+  int touched[2] = {0, 0};
+  for (int c = 0; c < 2; ++c)
+    for (int l = 0; l < 128; ++l)
+      for (int col = 0; col < 128; ++col) {
+        const float v = img[(c * 128 + l) * 128 + col];
+        if (std::isnan(v)) continue;
+        const int iv = (int)v;
+        map_m[(c * 128 + l) * 128 + col] = iv % 256; map_n[(c * 128 + l) * 128 + col] = iv / 256;
+        ++touched[c];
+      }
+  printf("mode %d coded: cells written CTA0 %d, CTA1 %d (of 16384 each)\n", mode, touched[0], touched[1]);
+  const int ls[8] = {0, 31, 32, 63, 64, 95, 96, 127}, cs[4] = {0, 63, 64, 127};
+  for (int c = 0; c < 2; ++c)
+    for (int li = 0; li < 8; ++li) {
+      printf("  CTA%d lane %3d:", c, ls[li]);
+      for (int ci = 0; ci < 4; ++ci) {
+        const int idx = (c * 128 + ls[li]) * 128 + cs[ci];
+        if (map_m[idx] < 0) printf("  col %3d -> (untouched)", cs[ci]);
+        else printf("  col %3d -> (m %3d, n %3d)", cs[ci], map_m[idx], map_n[idx]);
+      }
+      printf("\n");
+    }
+  // every (m, n) must appear exactly once
+  std::vector<int> seen((size_t)pc.M * 128, 0);
+  for (size_t i = 0; i < map_m.size(); ++i)
+    if (map_m[i] >= 0 && map_m[i] < pc.M && map_n[i] >= 0 && map_n[i] < 128) ++seen[map_m[i] * 128 + map_n[i]];
+  int miss = 0, dup = 0;
+  for (int v : seen) { miss += (v == 0); dup += (v > 1); }
+  printf("mode %d coded: %d (m,n) missing, %d duplicated\n", mode, miss, dup);
+  // 2. random run verified through the discovered map
+  Problem pr = make_problem(mode, false);
+  img = run_layout(mode, pr);
+  int bad = 0, checked = 0;
+  for (size_t i = 0; i < map_m.size(); ++i) {
+    if (map_m[i] < 0 || map_m[i] >= pr.M || map_n[i] >= 128) continue;
+    ++checked;
+    const float want = pr.ref[map_m[i] * 128 + map_n[i]];
+    if (img[i] != want) { if (bad < 6) printf("  cell %zu (m %d n %d) got %f want %f\n", i, map_m[i], map_n[i], img[i], want); ++bad; }
+  }
+  const bool ok = !bad && !miss && !dup && checked == pr.M * 128;
+  printf("probe2 mode %d: %s (%d checked, %d mismatches)\n", mode, ok ? "PASS" : "FAIL", checked, bad);
+  return ok ? 0 : 1;
+}

@@ -6,6 +6,9 @@
 //   2: D[128x128] = P[128xK=128] * V[K=128 x 128]      TS, A = P written to TMEM by tcgen05.st
 //   3: D[128x128] = A^T ... A MN-major: D = At[K=128 x 128]^T * V[K x 128]  (dS^T-style operand)
 //   4: fp32 TMA reduce-add of a smem tile into global (dQ accumulation path)
+//   5/6: D[128x128] = A[128 x K=16] * B[128 x K=16]^T with both operands in the NO-SWIZZLE K-major
+//        canonical layout (8-row x 16-byte core matrices), written by st.shared: which descriptor field
+//        is the K-direction core stride?  5: LBO = K stride (128), SBO = 8-row-group stride (256); 6: swapped
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -134,6 +137,50 @@ reduce_probe_kernel(const __grid_constant__ CUtensorMap tmD) {
   }
 }
 
+
+// modes 5/6: no-swizzle K-major operands.  element (r, k) of a [128 x 16] tile lives at
+//   (r / 8) * 256 + (k / 8) * 128 + (r % 8) * 16 + (k % 8) * 2
+__device__ __forceinline__ uint64_t make_desc_noswz(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  return d;  // layout type 0 = no swizzle
+}
+__global__ void __launch_bounds__(128, 1)
+noswz_probe_kernel(const __nv_bfloat16 *a, const __nv_bfloat16 *b, float *d_out, int swapped) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t *bar_mma = (uint64_t *)(smem + 8192);
+  uint32_t *tptr = (uint32_t *)(bar_mma + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, r = threadIdx.x;
+  if (threadIdx.x == 0) { mbar_init(bar_mma, 1); fence_barrier_init(); }
+  if (warp == 1) tmem_alloc<128>(tptr);
+  for (int kc = 0; kc < 2; ++kc) {
+    *(uint4 *)(smem + (r / 8) * 256 + kc * 128 + (r % 8) * 16) = *(const uint4 *)(a + r * 16 + kc * 8);
+    *(uint4 *)(smem + 4096 + (r / 8) * 256 + kc * 128 + (r % 8) * 16) = *(const uint4 *)(b + r * 16 + kc * 8);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before(); __syncthreads(); tc_fence_after();
+  const uint32_t tb = *tptr;
+  if (threadIdx.x == 0) {
+    const uint32_t lbo = swapped ? 256 : 128, sbo = swapped ? 128 : 256;
+    umma_ss(tb, make_desc_noswz(smem_u32(smem), lbo, sbo), make_desc_noswz(smem_u32(smem + 4096), lbo, sbo),
+            make_idesc(128, 128, 1, 0, 0), 0);
+    umma_commit(bar_mma);
+  }
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[32];
+    tmem_ld32(tb + ((uint32_t)(warp * 32) << 16) + c * 32, v);
+    tmem_ld_wait();
+    for (int e = 0; e < 32; ++e) d_out[(warp * 32 + lane) * 128 + c * 32 + e] = __uint_as_float(v[e]);
+  }
+  tc_fence_before(); __syncthreads();
+  if (warp == 1) tmem_dealloc<128>(tb);
+}
+
 int main(int argc, char **argv) {
   const int mode = argc > 1 ? atoi(argv[1]) : 0;
   const int N = 128;
@@ -147,6 +194,27 @@ int main(int argc, char **argv) {
     int bad = 0;
     for (int i = 0; i < N * N; ++i) if (h[i] != 2.f * i) { if (bad < 5) printf("  [%d] got %f want %f\n", i, h[i], 2.f * i); ++bad; }
     printf("probe mode 4: %s (%d mismatches)\n", bad ? "FAIL" : "PASS", bad);
+    return bad ? 1 : 0;
+  }
+  if (mode == 5 || mode == 6) {
+    std::vector<__nv_bfloat16> A(N * 16), B(N * 16);
+    std::vector<float> Af(N * 16), Bf(N * 16);
+    srand(9);
+    for (int i = 0; i < N * 16; ++i) { Af[i] = (float)(rand() % 7 - 3); Bf[i] = (float)(rand() % 5 - 2); A[i] = __float2bfloat16(Af[i]); B[i] = __float2bfloat16(Bf[i]); }
+    __nv_bfloat16 *dA, *dB; float *dD;
+    CK(cudaMalloc(&dA, N * 16 * 2)); CK(cudaMalloc(&dB, N * 16 * 2)); CK(cudaMalloc(&dD, N * N * 4));
+    CK(cudaMemcpy(dA, A.data(), N * 16 * 2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dB, B.data(), N * 16 * 2, cudaMemcpyHostToDevice));
+    noswz_probe_kernel<<<1, 128, 9216>>>(dA, dB, dD, mode == 6);
+    CK(cudaDeviceSynchronize());
+    std::vector<float> h(N * N); CK(cudaMemcpy(h.data(), dD, N * N * 4, cudaMemcpyDeviceToHost));
+    int bad = 0;
+    for (int m = 0; m < N; ++m) for (int n = 0; n < N; ++n) {
+      float sref = 0; for (int k = 0; k < 16; ++k) sref += Af[m * 16 + k] * Bf[n * 16 + k];
+      if (h[m * N + n] != sref) { if (bad < 4) printf("  [%d,%d] got %f want %f\n", m, n, h[m * N + n], sref); ++bad; }
+    }
+    printf("probe mode %d (no-swizzle K-major, %s): %s (%d mismatches)\n", mode,
+           mode == 5 ? "LBO=K-core stride 128, SBO=row-group stride 256" : "LBO=256, SBO=128", bad ? "FAIL" : "PASS", bad);
     return bad ? 1 : 0;
   }
   std::vector<__nv_bfloat16> A(N * N), B(N * N);
