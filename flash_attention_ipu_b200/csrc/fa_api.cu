@@ -293,8 +293,9 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
 size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 int lq_pad(const fa_b200_problem *p) { return (p->Lq + 127) / 128 * 128; }
 // workspace: delta[G][Lq_pad] | lse2[G][Lq_pad] | dq_acc[G][Lq][D] (fp32), each 256-byte aligned
+// (FA_BWD_STATS_MMA: the two statistics are 32-byte operand-slab rows instead of one float each)
 size_t ws_stat_bytes(const fa_b200_problem *p) {
-  return align256((size_t)p->B * p->H * lq_pad(p) * sizeof(float));
+  return align256((size_t)p->B * p->H * lq_pad(p) * (fa::kStatsMma ? 32 : sizeof(float)));
 }
 
 template <int D, bool kBf16>
@@ -311,7 +312,8 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   fa::fa_bwd_prep_kernel<T, D><<<blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st>>>(
       reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
       reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
-      delta, lse2, dq_acc, p->B, p->H, p->Lq, Lp);
+      delta, lse2, dq_acc, p->B, p->H, p->Lq, Lp, /*slab_lse=*/ws + ws_stat_bytes(p), /*slab_delta=*/ws,
+      1.f / p->softmax_scale);
   if (int rc = launched()) return rc;
 
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
@@ -326,6 +328,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
   bp.lse2 = lse2; bp.delta = delta;
+  bp.slab_delta = ws; bp.slab_lse = ws + ws_stat_bytes(p);
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
   bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;
   bp.causal = p->causal; bp.shift = p->q_pos0 - p->kv_pos0;

@@ -24,6 +24,9 @@
 //   warps 8-11 : dQ drain (TMEM -> regs -> smem -> TMA reduce-add)
 //   warp 12 TMA producer | warp 13 MMA issuer | warp 14 TMEM alloc | warp 15 idle
 #pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <type_traits>
 #include "fa_fwd_sm100.cuh"
 
 namespace fa {
@@ -32,11 +35,29 @@ constexpr int kBwdThreads = 512;
 #ifndef FA_BWD_POLY_PAIRS
 #define FA_BWD_POLY_PAIRS 12
 #endif
-constexpr int kBwdPolyPairs = FA_BWD_POLY_PAIRS;  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
+constexpr int kBwdPolyPairs = FA_BWD_POLY_PAIRS;
+// FA_BWD_STATS_MMA: the per-query statistics (-lse, -delta) are added to S^T and dP^T by the TENSOR
+// CORE as one extra K=16 step each (A = a constant [1 1 1 0 ...] slab, B = a [128 q x 16] slab holding
+// the statistic split into three 16-bit terms, both in the no-swizzle K-major layout) instead of
+// being read by every compute thread with broadcast LDS.128: those loads are 1016 of the 4270
+// shared-memory wavefronts per Q tile that bound the kernel (profiles/r01_v6_ncu_bwd.txt); the
+// extra MMA steps cost 128.  The slabs take 16 KB, which the dQ staging ring gives up (one 4 KB
+// slab per drain warp instead of two).
+#ifndef FA_BWD_STATS_MMA
+#define FA_BWD_STATS_MMA 0
+#endif
+constexpr bool kStatsMma = FA_BWD_STATS_MMA != 0;
+#ifndef FA_BWD_DRAIN_SINGLE
+#define FA_BWD_DRAIN_SINGLE FA_BWD_STATS_MMA
+#endif
+constexpr bool kDrainSingle = FA_BWD_DRAIN_SINGLE != 0;  // one 4 KB staging slab per drain warp instead of two  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
 
 struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
   const float *delta;  // [G][Lq_pad]  -rowsum(O o dO); 0 for padding
+  // FA_BWD_STATS_MMA: the same two statistics as ready-made shared-memory images, one 4 KB slab per
+  // 128-row Q tile ([G][Lq_pad / 128][4096] bytes each; see fa_bwd_prep_kernel)
+  const uint8_t *slab_lse, *slab_delta;
   int Lq, Lk, H, Lq_pad;
   int Hkv, kv_ratio;   // K/V heads and query heads per K/V head (H = Hkv * kv_ratio; 1 = multi-head)
   int causal, shift;
@@ -56,9 +77,13 @@ struct BwdSmem {
   static constexpr int kQOff = kVOff + kTileBytes;            // 2 stages (epilogue: dK | dV staging)
   static constexpr int kDOOff = kQOff + 2 * kTileBytes;       // 1 stage
   static constexpr int kDSOff = kDOOff + kTileBytes;          // dS^T [128 keys][128 q] bf16
-  static constexpr int kDQOff = kDSOff + 2 * kHalfBytes;      // fp32 staging [128 q][64 d]
-  static constexpr int kStatOff = kDQOff + 2 * kHalfBytes;    // 2 stages x (lse2[128] | delta[128])
-  static constexpr int kBarOff = kStatOff + 2 * 1024;
+  static constexpr int kDQOff = kDSOff + 2 * kHalfBytes;      // fp32 staging: 4 drain warps x kDrainSlabs x 4 KB
+  static constexpr int kDrainSlabs = kDrainSingle ? 1 : 2;
+  static constexpr int kStatOff = kDQOff + 4 * kDrainSlabs * 4096;
+  // !kStatsMma: 2 stages x (lse2[128] | delta[128]) fp32.   kStatsMma: four 4 KB no-swizzle K-major
+  // [128 x 16] operand slabs: lse (stage 0, 1; travel with Q), delta (travels with dO), ones
+  static constexpr int kSlabLseOff = kStatOff, kSlabDeltaOff = kStatOff + 2 * 4096, kSlabOnesOff = kStatOff + 3 * 4096;
+  static constexpr int kBarOff = kStatOff + (kStatsMma ? 4 * 4096 : 2 * 1024);
   static constexpr int kNumBars = 16;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kBytes = kTmemPtrOff + 16;
@@ -140,6 +165,14 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     mbar_init(dq_full, 1); mbar_init(dq_empty, 4); mbar_init(dkv_full, 1);
     fence_barrier_init();
   }
+  if (kStatsMma && threadIdx.x < 128) {
+    // constant A operand of the two statistic steps: row r = [1 1 1 0 0 0 0 0 | 0 x 8] (16-bit floats)
+    constexpr uint32_t kOne = kBf16 ? 0x3F80u : 0x3C00u;
+    uint8_t *row = smem + L::kSlabOnesOff + (threadIdx.x >> 3) * 256 + (threadIdx.x & 7) * 16;
+    *reinterpret_cast<uint4 *>(row) = make_uint4(kOne | (kOne << 16), kOne, 0u, 0u);
+    *reinterpret_cast<uint4 *>(row + 128) = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async_smem();
+  }
   if (warp == 14) tmem_alloc<512>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
@@ -168,16 +201,22 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           continue;
         }
 #endif
-        mbar_arrive_expect_tx(&q_full[s], L::kTileBytes + 1024);
+        const size_t slab = (static_cast<size_t>(b * p.H + h) * (p.Lq_pad >> 7) + i) * 4096;
+        mbar_arrive_expect_tx(&q_full[s], L::kTileBytes + (kStatsMma ? 4096 : 1024));
         for (int hh = 0; hh < kHalves; ++hh)
           tma_load_4d(&tmQ, &q_full[s], smem + L::kQOff + s * L::kTileBytes + hh * L::kHalfBytes,
                       hh * 64, i * 128, h, b);
-        bulk_load_1d(smem + L::kStatOff + s * 1024, lse_g + i * 128, 512, &q_full[s]);
-        bulk_load_1d(smem + L::kStatOff + s * 1024 + 512, delta_g + i * 128, 512, &q_full[s]);
+        if (kStatsMma) {
+          bulk_load_1d(smem + L::kSlabLseOff + s * 4096, p.slab_lse + slab, 4096, &q_full[s]);
+        } else {
+          bulk_load_1d(smem + L::kStatOff + s * 1024, lse_g + i * 128, 512, &q_full[s]);
+          bulk_load_1d(smem + L::kStatOff + s * 1024 + 512, delta_g + i * 128, 512, &q_full[s]);
+        }
         mbar_wait(do_empty, (it & 1) ^ 1);
-        mbar_arrive_expect_tx(do_full, L::kTileBytes);
+        mbar_arrive_expect_tx(do_full, L::kTileBytes + (kStatsMma ? 4096 : 0));
         for (int hh = 0; hh < kHalves; ++hh)
           tma_load_4d(&tmDO, do_full, smem + L::kDOOff + hh * L::kHalfBytes, hh * 64, i * 128, h, b);
+        if (kStatsMma) bulk_load_1d(smem + L::kSlabDeltaOff, p.slab_delta + slab, 4096, do_full);
       }
     }
   } else if (warp == 13) {
@@ -205,19 +244,27 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint32_t tDK = tmem_base + kColDK, tDV = tmem_base + kColDV;
       const bool leader = elect_one();
 
-      auto issue_kk = [&](uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo) {
+      // no-swizzle K-major [128 x 16] slabs: LBO = 128 (next 8 K elements), SBO = 256 (next 8 rows)
+      // (tests/cuda/umma_probe.cu mode 5)
+      constexpr uint32_t hi_ns = ((256u >> 4) & 0x3FFFu) | (1u << 14);
+      const uint32_t ones_ns = smem_desc_lo(smem_u32(smem + L::kSlabOnesOff), 128);
+      const uint32_t lse_ns = smem_desc_lo(smem_u32(smem + L::kSlabLseOff), 128);
+      const uint32_t delta_ns = smem_desc_lo(smem_u32(smem + L::kSlabDeltaOff), 128);
+      // d = a b^T (+ 1 stat^T: the per-query statistic added to every key row by one more K step)
+      auto issue_kk = [&](uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t stat_lo) {
         #pragma unroll
         for (int k = 0; k < D / 16; ++k) {
           const uint32_t off = ((k / 4) * L::kHalfBytes + (k % 4) * 32) >> 4;
           umma_ss2(d_tmem, a_lo + off, hi, b_lo + off, hi, idesc_kk, k > 0);
         }
+        if (kStatsMma) umma_ss2(d_tmem, ones_ns, hi_ns, stat_lo, hi_ns, idesc_kk, 1);
       };
 
       mbar_wait(kv_full, 0);
       mbar_wait(&q_full[0], 0);
       tc_fence_after();
       if (leader) {
-        issue_kk(tS, k_kmaj, q_kmaj);  // S^T(0)
+        issue_kk(tS, k_kmaj, q_kmaj, lse_ns);  // S^T(0)
         umma_commit(s_full);
       }
 #ifdef FA_BWD_TRACE
@@ -244,7 +291,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (it > 0) FA_BT_WAIT(1, mbar_wait(dq_empty, (it - 1) & 1));
         tc_fence_after();
         if (leader) {
-          issue_kk(tDP, v_kmaj, do_kmaj);
+          issue_kk(tDP, v_kmaj, do_kmaj, delta_ns);
           umma_commit(dp_full);
           umma_commit(do_empty);
         }
@@ -252,7 +299,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           FA_BT_WAIT(3, mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1));
           tc_fence_after();
           if (leader) {
-            issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16);
+            issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16, lse_ns + ((it + 1) & 1) * (4096 >> 4));
             umma_commit(s_full);
           }
         }
@@ -280,7 +327,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (it > 0) FA_BT_WAIT(1, mbar_wait(dq_empty, (it - 1) & 1));
         tc_fence_after();
         if (leader) {
-          issue_kk(tDP, v_kmaj, do_kmaj);
+          issue_kk(tDP, v_kmaj, do_kmaj, delta_ns);
           umma_commit(dp_full);
         }
         // dV += P^T dO
@@ -298,7 +345,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           FA_BT_WAIT(3, mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1));
           tc_fence_after();
           if (leader) {
-            issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16);
+            issue_kk(tS, k_kmaj, q_kmaj + ((it + 1) & 1) * kTile16, lse_ns + ((it + 1) & 1) * (4096 >> 4));
             umma_commit(s_full);
           }
         }
@@ -339,10 +386,47 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     reg_dealloc<104>();
     const int w = warp & 3;
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
-    uint8_t *wstage = smem + L::kDQOff + w * 8192;
+    uint8_t *wstage = smem + L::kDQOff + w * (L::kDrainSlabs * 4096);
     for (int it = 0, h = h0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(h, i, i0, num_q_tiles)) {
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
+      if (kDrainSingle) {
+        // One 4 KB slab (32 fp32 columns) per warp: a round = wait until the previous reduce has
+        // read the slab, store 32 columns, reduce.  Two rounds of columns are held in registers, so
+        // dQ has left TMEM (dq_empty) once the slabs of rounds 0 .. D/32-3 are on their way.
+        constexpr int kRounds = D / 32;
+        uint32_t r[2][32];
+        tmem_ld32(tDQ, r[0]);
+        tmem_ld32(tDQ + 32, r[1]);
+        #pragma unroll
+        for (int q = 0; q < kRounds; ++q) {
+          if (q + 2 <= kRounds) {  // a load is outstanding: initial pair, or the one issued last round
+            tmem_ld_wait();
+            if (q + 2 == kRounds) { tc_fence_before(); mbar_arrive_warp(dq_empty); }
+          }
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+#ifndef FA_EXPERIMENT_NO_DRAIN_STS
+          #pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 v4 = make_uint4(r[q & 1][c * 4], r[q & 1][c * 4 + 1], r[q & 1][c * 4 + 2], r[q & 1][c * 4 + 3]);
+            *reinterpret_cast<uint4 *>(wstage + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
+          }
+#else
+          asm volatile("" ::"r"(r[q & 1][0]), "r"(r[q & 1][31]));
+#endif
+          if (q + 2 < kRounds) tmem_ld32(tDQ + (q + 2) * 32, r[q & 1]);
+          fence_proxy_async_smem();
+          __syncwarp();
+#ifndef FA_EXPERIMENT_NO_DRAIN_STS
+          if (lane == 0) {
+            tma_reduce_add_4d(&tmDQ, wstage, q * 32, i * 128 + w * 32, h, b);
+            tma_store_commit();
+          }
+#endif
+        }
+        continue;
+      }
       // 64 fp32 columns (two 32-column slabs, one per staging buffer) at a time.  The TMEM reads of
       // the next half are issued as soon as this half's registers have been stored, so dQ leaves
       // TMEM (dq_empty -> the MMA warp may overwrite it with dP^T(it+1)) after two loads, one
@@ -397,14 +481,17 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
     for (int it = 0, hx = 0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(hx, i, i0, num_q_tiles)) {
       const float4 *stat = reinterpret_cast<const float4 *>(smem + L::kStatOff + (it & 1) * 1024) + wg * 16;
-      mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
       // -lse2 of this warpgroup's 64 query columns: loaded (broadcast LDS.128) BEFORE the S^T wait so
-      // that the shared-memory latency hides behind it
-      float nl[64];
-      #pragma unroll
-      for (int c4 = 0; c4 < 16; ++c4) {
-        const float4 l4 = stat[c4];
-        nl[4 * c4] = l4.x; nl[4 * c4 + 1] = l4.y; nl[4 * c4 + 2] = l4.z; nl[4 * c4 + 3] = l4.w;
+      // that the shared-memory latency hides behind it.  (kStatsMma: the tensor core has already
+      // added -lse / softmax_scale to S^T and -delta to dP^T; nothing to load.)
+      float nl[kStatsMma ? 2 : 64];
+      if (!kStatsMma) {
+        mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
+        #pragma unroll
+        for (int c4 = 0; c4 < (kStatsMma ? 0 : 16); ++c4) {
+          const float4 l4 = stat[c4];
+          nl[4 * c4] = l4.x; nl[4 * c4 + 1] = l4.y; nl[4 * c4 + 2] = l4.z; nl[4 * c4 + 3] = l4.w;
+        }
       }
       mbar_wait(s_full, it & 1);
       tc_fence_after();
@@ -422,8 +509,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           #pragma unroll
           for (int c = 0; c < 64; c += 2) {
             float x0, x1;
-            f2_unpack(f2_fma(f2_pack(s[c >> 5][c & 31], s[c >> 5][(c & 31) + 1]), c2, f2_pack(nl[c], nl[c + 1])),
-                      x0, x1);
+            if (kStatsMma)
+              f2_unpack(f2_mul(f2_pack(s[c >> 5][c & 31], s[c >> 5][(c & 31) + 1]), c2), x0, x1);
+            else
+              f2_unpack(f2_fma(f2_pack(s[c >> 5][c & 31], s[c >> 5][(c & 31) + 1]), c2,
+                               f2_pack(nl[kStatsMma ? 0 : c], nl[kStatsMma ? 1 : c + 1])), x0, x1);
             const int pair = c >> 1;
             if (decltype(poly_first)::value ? pair < kBwdPolyPairs : pair >= 32 - kBwdPolyPairs) {
               poly_exp2_pair(x0, x1, pr[c], pr[c + 1]);
@@ -453,9 +543,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       // dS^T = P^T o (dP^T - delta); -delta of each 32-column half is fetched ahead of the
       // barrier / TMEM load it is used after
-      float nd[32];
+      float nd[kStatsMma ? 2 : 32];
       #pragma unroll
-      for (int c4 = 0; c4 < 8; ++c4) {
+      for (int c4 = 0; c4 < (kStatsMma ? 0 : 8); ++c4) {
         const float4 d4 = stat[32 + c4];
         nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
       }
@@ -470,13 +560,17 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         #pragma unroll
         for (int c = 0; c < 32; c += 2) {
           float a0, a1;
-          f2_unpack(f2_mul(f2_pack(pr[hf * 32 + c], pr[hf * 32 + c + 1]),
-                           f2_add(f2_pack(dp[c], dp[c + 1]), f2_pack(nd[c], nd[c + 1]))), a0, a1);
+          if (kStatsMma)
+            f2_unpack(f2_mul(f2_pack(pr[hf * 32 + c], pr[hf * 32 + c + 1]), f2_pack(dp[c], dp[c + 1])), a0, a1);
+          else
+            f2_unpack(f2_mul(f2_pack(pr[hf * 32 + c], pr[hf * 32 + c + 1]),
+                             f2_add(f2_pack(dp[c], dp[c + 1]),
+                                    f2_pack(nd[kStatsMma ? 0 : c], nd[kStatsMma ? 1 : c + 1]))), a0, a1);
           w[c >> 1] = pack2<kBf16>(a0, a1);
         }
-        if (hf == 0) {
+        if (hf == 0 && !kStatsMma) {
           #pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) {
+          for (int c4 = 0; c4 < (kStatsMma ? 0 : 8); ++c4) {
             const float4 d4 = stat[40 + c4];
             nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
           }
@@ -561,7 +655,8 @@ template <typename T, int D>
 __global__ void __launch_bounds__(256)
 fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T *dout, int64_t d_sb,
                    int64_t d_sh, int64_t d_sl, const float *lse, float *delta, float *lse2,
-                   float *dq_acc, int B, int H, int Lq, int Lq_pad) {
+                   float *dq_acc, int B, int H, int Lq, int Lq_pad, uint8_t *slab_lse = nullptr,
+                   uint8_t *slab_delta = nullptr, float inv_scale = 1.f) {
   constexpr int kTpr = D / 8;  // threads per row
   const int sub = threadIdx.x % kTpr;
   const int64_t rid = static_cast<int64_t>(blockIdx.x) * (256 / kTpr) + threadIdx.x / kTpr;
@@ -586,6 +681,31 @@ fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T
   }
   #pragma unroll
   for (int off = kTpr / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+  if (kStatsMma) {
+    // the statistics as [128 q x 16] no-swizzle K-major operand slabs (one 4 KB image per Q tile):
+    // row q = [hi mid lo 0 0 0 0 0 | 0 x 8] with hi + mid + lo = -lse / softmax_scale (resp. -delta)
+    // to 3 x the mantissa of T; rows that must give P = 0 carry a huge negative value instead of -inf
+    // (inf x 0 inside the MMA would be NaN)
+    if (in_range && sub == 0) {
+      const float big = std::is_same<T, __half>::value ? -60000.f : -1e30f;
+      const float vals[2] = {l2 == -INFINITY ? big : l2 * (inv_scale / kLog2e), -s};  // l2 = -lse * log2(e)
+      uint8_t *dst[2] = {slab_lse, slab_delta};
+      const size_t off = static_cast<size_t>(rid >> 7) * 4096 + ((rid & 127) >> 3) * 256 + (rid & 7) * 16;
+      #pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        const T hi = static_cast<T>(vals[w]);
+        const float r1 = vals[w] - static_cast<float>(hi);
+        const T mid = static_cast<T>(r1);
+        const T lo = static_cast<T>(r1 - static_cast<float>(mid));
+        const uint32_t w0 = static_cast<uint32_t>(*reinterpret_cast<const unsigned short *>(&hi)) |
+                            (static_cast<uint32_t>(*reinterpret_cast<const unsigned short *>(&mid)) << 16);
+        const uint32_t w1 = *reinterpret_cast<const unsigned short *>(&lo);
+        *reinterpret_cast<uint4 *>(dst[w] + off) = make_uint4(w0, w1, 0u, 0u);
+        *reinterpret_cast<uint4 *>(dst[w] + off + 128) = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    return;
+  }
   if (in_range && sub == 0) { delta[rid] = -s; lse2[rid] = l2; }
 }
 
