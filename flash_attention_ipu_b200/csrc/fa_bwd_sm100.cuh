@@ -461,7 +461,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #if !defined(FA_EXPERIMENT_NO_REDUCE) && !defined(FA_EXPERIMENT_NO_DRAIN_STS)
         if (lane == 0) {
           tma_reduce_add_4d(&tmDQ, wstage, hh * 64, i * 128 + w * 32, h, b);
+#ifndef FA_EXPERIMENT_HALF_REDUCE  // (timing experiment only when defined: wrong results)
           tma_reduce_add_4d(&tmDQ, wstage + 4096, hh * 64 + 32, i * 128 + w * 32, h, b);
+#endif
           tma_store_commit();
         }
 #endif
