@@ -16,7 +16,8 @@ _DTYPES = {torch.float16: FA_B200_F16, torch.bfloat16: FA_B200_BF16, torch.float
 
 EXPORTED_SYMBOLS = (
     "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_merge", "fa_b200_merge_acc",
-    "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_last_error", "fa_b200_version",
+    "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
+    "fa_b200_version",
 )
 
 
@@ -49,6 +50,8 @@ _lib.fa_b200_kernel_family.argtypes = [_PP]
 _lib.fa_b200_kernel_family.restype = c_int
 _lib.fa_b200_launch_count.argtypes = []
 _lib.fa_b200_launch_count.restype = c_int64
+_lib.fa_b200_tmap_cache_stats.argtypes = [POINTER(c_int64), POINTER(c_int64)]
+_lib.fa_b200_tmap_cache_stats.restype = None
 _lib.fa_b200_last_error.argtypes = []
 _lib.fa_b200_last_error.restype = c_char_p
 _lib.fa_b200_version.argtypes = []
@@ -61,6 +64,13 @@ def library_path() -> str:
 
 def launch_count() -> int:
     return int(_lib.fa_b200_launch_count())
+
+
+def tmap_cache_stats() -> tuple:
+    """(hits, misses) of the shim's TMA-descriptor cache since the library was loaded."""
+    hits, misses = c_int64(0), c_int64(0)
+    _lib.fa_b200_tmap_cache_stats(byref(hits), byref(misses))
+    return int(hits.value), int(misses.value)
 
 
 def version() -> int:

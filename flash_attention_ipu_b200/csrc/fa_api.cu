@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <type_traits>
 
 #include "../../include/fa_b200.h"
@@ -96,9 +97,55 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
+// Tensor-map cache: a training loop calls with the same (pointer, shape, strides) step after step
+// (torch's caching allocator hands the same blocks back), and cuTensorMapEncodeTiled is the largest
+// host cost of a launch once the ops are registered natively (4 maps per forward, 7 per backward).
+// A CUtensorMap is a plain 128-byte value that depends only on the key below, so a hit is a copy.
+// Unified addressing makes the pointer unique across devices.  Guarded by one mutex; the library
+// stays re-entrant.
+struct TmapKey {
+  const void *ptr;
+  int64_t sb, sh, sl;
+  int32_t dtype, B, H, L, D, box_rows;
+};
+struct TmapSlot {
+  TmapKey key;
+  CUtensorMap map;
+};
+constexpr int kTmapSlots = 64;
+std::mutex g_tmap_mu;
+TmapSlot g_tmap[kTmapSlots];
+int g_tmap_used = 0, g_tmap_next = 0;
+std::atomic<int64_t> g_tmap_hits{0}, g_tmap_misses{0};
+
+bool tmap_lookup(const TmapKey &k, CUtensorMap *m) {
+  std::lock_guard<std::mutex> lock(g_tmap_mu);
+  for (int i = 0; i < g_tmap_used; ++i) {
+    const TmapKey &c = g_tmap[i].key;
+    if (c.ptr == k.ptr && c.sb == k.sb && c.sh == k.sh && c.sl == k.sl && c.dtype == k.dtype && c.B == k.B &&
+        c.H == k.H && c.L == k.L && c.D == k.D && c.box_rows == k.box_rows) {
+      *m = g_tmap[i].map;
+      return true;
+    }
+  }
+  return false;
+}
+void tmap_insert(const TmapKey &k, const CUtensorMap &m) {
+  std::lock_guard<std::mutex> lock(g_tmap_mu);
+  const int i = g_tmap_used < kTmapSlots ? g_tmap_used++ : (g_tmap_next++ % kTmapSlots);  // round-robin eviction
+  g_tmap[i].key = k;
+  g_tmap[i].map = m;
+}
+
 // (B,H,L,D) tensor, box = 128 bytes of D x `box_rows` rows, 128B swizzle.
 int make_tmap(CUtensorMap *m, const fa_b200_tensor *t, int dtype, int B, int H, int L, int D,
               int box_rows) {
+  const TmapKey key{t->ptr, t->stride_b, t->stride_h, t->stride_l, dtype, B, H, L, D, box_rows};
+  if (tmap_lookup(key, m)) {
+    g_tmap_hits.fetch_add(1, std::memory_order_relaxed);
+    return 0;
+  }
+  g_tmap_misses.fetch_add(1, std::memory_order_relaxed);
   EncodeTiledFn fn = encode_fn();
   if (!fn) return fail(FA_B200_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
   const size_t es = elem_size(dtype);
@@ -117,6 +164,7 @@ int make_tmap(CUtensorMap *m, const fa_b200_tensor *t, int dtype, int B, int H, 
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(FA_B200_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+  tmap_insert(key, *m);
   return 0;
 }
 
@@ -374,6 +422,10 @@ extern "C" {
 const char *fa_b200_last_error(void) { return g_err; }
 int fa_b200_version(void) { return 100; }
 int64_t fa_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+void fa_b200_tmap_cache_stats(int64_t *hits, int64_t *misses) {
+  if (hits) *hits = g_tmap_hits.load(std::memory_order_relaxed);
+  if (misses) *misses = g_tmap_misses.load(std::memory_order_relaxed);
+}
 
 int fa_b200_kernel_family(const fa_b200_problem *p) {
   if (int rc = check_problem(p)) return rc;

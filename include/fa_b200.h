@@ -106,6 +106,10 @@ int fa_b200_kernel_family(const fa_b200_problem *p);
 /* Number of kernel launches the library has enqueued since load (all threads). */
 int64_t fa_b200_launch_count(void);
 
+/* Tensor-map (TMA descriptor) cache of the shim: descriptors are keyed by (pointer, dtype, shape,
+ * strides, box) and reused across calls; counters since load (all threads). */
+void fa_b200_tmap_cache_stats(int64_t *hits, int64_t *misses);
+
 const char *fa_b200_last_error(void);
 int fa_b200_version(void);
 

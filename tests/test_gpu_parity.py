@@ -444,3 +444,19 @@ def test_config1_full_size_fp32():
             mod.uninstall()
     assert (out.detach().cpu() - ref.detach()).abs().max().item() <= 2e-5
     assert (x.grad.cpu() - xr.grad).abs().max().item() <= 1e-4
+
+
+@pytest.mark.gpu
+def test_tensor_map_cache_reuses_descriptors():
+    """The shim caches TMA descriptors by (pointer, dtype, shape, strides, box): a second call on the
+    same buffers must not encode again, and must give the same result (threading row)."""
+    import flash_attention_ipu as fa
+    from flash_attention_ipu_b200._impl import native
+    torch.manual_seed(7)
+    qkv = torch.randn(3, 2, 256, 128, device="cuda", dtype=torch.bfloat16)
+    out1 = fa.flash_attention_qkv_packed(qkv, 2, 2).clone()
+    h0, m0 = native.tmap_cache_stats()
+    out2 = fa.flash_attention_qkv_packed(qkv, 2, 2)
+    h1, m1 = native.tmap_cache_stats()
+    assert h1 - h0 >= 3, "q, k, v descriptors were re-encoded"
+    assert torch.equal(out1, out2)
