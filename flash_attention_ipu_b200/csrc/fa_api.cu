@@ -406,6 +406,8 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
     cudaMemcpy(h, d_btrace, sizeof(h), cudaMemcpyDeviceToHost);
     fprintf(stderr, "bwd trace (CTA 0, MMA warp, clk per iteration): do_full %.0f dq_empty %.0f p_full %.0f q_full %.0f ds_full %.0f | loop %.0f (n=%llu)\n",
             (double)h[0] / h[6], (double)h[1] / h[6], (double)h[2] / h[6], (double)h[3] / h[6], (double)h[4] / h[6], (double)h[5] / h[6], h[6]);
+    fprintf(stderr, "bwd trace (CTA 0, drain warp 0, clk per iteration): wait dq_full %.0f | dq_full->dq_empty %.0f | wait_read before half 0 %.0f, before half 1 %.0f\n",
+            (double)h[10] / h[6], (double)h[11] / h[6], (double)h[8] / h[6], (double)h[9] / h[6]);
   }
 #endif
   // dQ = softmax_scale * dq_acc, cast to the output dtype

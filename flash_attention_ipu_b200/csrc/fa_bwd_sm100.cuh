@@ -50,7 +50,17 @@ constexpr bool kStatsMma = FA_BWD_STATS_MMA != 0;
 #ifndef FA_BWD_DRAIN_SINGLE
 #define FA_BWD_DRAIN_SINGLE FA_BWD_STATS_MMA
 #endif
-constexpr bool kDrainSingle = FA_BWD_DRAIN_SINGLE != 0;  // one 4 KB staging slab per drain warp instead of two  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
+constexpr bool kDrainSingle = FA_BWD_DRAIN_SINGLE != 0;
+// FA_BWD_DRAIN_PIPE: the two 4 KB staging slabs of a drain warp are re-filled one at a time, each
+// reduce-add in its own bulk group and `wait_group.read 1` before a slab is written again, so the
+// reduce engine always has the other slab queued while this one is staged.  (The default stages
+// two slabs, issues two reduces and then waits for BOTH to be read: the trace build shows that
+// wait at 1 300 clk per iteration and the drain warp busy 93 % of the time -- it, not the tensor
+// pipe, paces the loop.)
+#ifndef FA_BWD_DRAIN_PIPE
+#define FA_BWD_DRAIN_PIPE 0
+#endif
+constexpr bool kDrainPipe = FA_BWD_DRAIN_PIPE != 0;  // one 4 KB staging slab per drain warp instead of two  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
 
 struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
@@ -388,7 +398,13 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
     uint8_t *wstage = smem + L::kDQOff + w * (L::kDrainSlabs * 4096);
     for (int it = 0, h = h0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(h, i, i0, num_q_tiles)) {
+#ifdef FA_BWD_TRACE
+      const long long tf0 = clock64();
+#endif
       mbar_wait(dq_full, it & 1);
+#ifdef FA_BWD_TRACE
+      if (blockIdx.x == 0 && w == 0 && lane == 0) p.trace[10] += clock64() - tf0;  // drain warp idle: waiting for dQ
+#endif
       tc_fence_after();
       if (kDrainSingle) {
         // One 4 KB slab (32 fp32 columns) per warp: a round = wait until the previous reduce has
@@ -427,6 +443,40 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         continue;
       }
+      if (kDrainPipe) {
+        constexpr int kSlabs = D / 32;
+        uint32_t r[2][32];
+        tmem_ld32(tDQ, r[0]);
+        tmem_ld32(tDQ + 32, r[1]);
+        #pragma unroll
+        for (int k = 0; k < kSlabs; ++k) {
+          if ((k & 1) == 0) {  // the loads of slabs k and k+1 were issued together
+            tmem_ld_wait();
+            if (k + 2 == kSlabs) { tc_fence_before(); mbar_arrive_warp(dq_empty); }
+          }
+          // this buffer was last used two bulk groups ago; the previous group (other buffer) may still be pending
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          uint8_t *slab = wstage + (k & 1) * 4096;
+          #pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 v4 = make_uint4(r[k & 1][c * 4], r[k & 1][c * 4 + 1], r[k & 1][c * 4 + 2], r[k & 1][c * 4 + 3]);
+            *reinterpret_cast<uint4 *>(slab + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
+          }
+          if (k + 2 < kSlabs) tmem_ld32(tDQ + (k + 2) * 32, r[k & 1]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_reduce_add_4d(&tmDQ, slab, k * 32, i * 128 + w * 32, h, b);
+            tma_store_commit();
+          }
+        }
+        continue;
+      }
+#ifdef FA_BWD_TRACE
+      const bool tr_on = blockIdx.x == 0 && w == 0 && lane == 0;
+      long long tq0 = clock64();
+#endif
       // 64 fp32 columns (two 32-column slabs, one per staging buffer) at a time.  The TMEM reads of
       // the next half are issued as soon as this half's registers have been stored, so dQ leaves
       // TMEM (dq_empty -> the MMA warp may overwrite it with dP^T(it+1)) after two loads, one
@@ -437,8 +487,19 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       #pragma unroll
       for (int hh = 0; hh < kHalves; ++hh) {
         tmem_ld_wait();
-        if (hh == kHalves - 1) { tc_fence_before(); mbar_arrive_warp(dq_empty); }
+        if (hh == kHalves - 1) {
+          tc_fence_before(); mbar_arrive_warp(dq_empty);
+#ifdef FA_BWD_TRACE
+          if (tr_on) p.trace[11] += clock64() - tq0;  // dq_full seen -> dq_empty arrived
+#endif
+        }
+#ifdef FA_BWD_TRACE
+        const long long tw0 = clock64();
+#endif
         if (lane == 0) tma_store_wait_read<0>();  // the reduces that last used the two buffers have read them
+#ifdef FA_BWD_TRACE
+        if (tr_on) p.trace[8 + hh] += clock64() - tw0;   // [8]: wait_read before half 0, [9]: before half 1
+#endif
         __syncwarp();
 #ifndef FA_EXPERIMENT_NO_DRAIN_STS  // (timing experiment only when defined: wrong results)
         #pragma unroll
