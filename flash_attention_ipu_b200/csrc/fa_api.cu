@@ -184,9 +184,17 @@ unsigned blocks_for(int64_t rows, int per_block) { return (unsigned)((rows + per
 // D <= 128: shared-memory tiled FFMA kernels (fa_tiled_simt.cuh); 128 < D <= 256: warp-per-row.
 unsigned tiles(int rows) { return (unsigned)((rows + fa::kTB - 1) / fa::kTB); }
 
+// The dynamic shared-memory opt-in is a per-DEVICE function attribute: `done` keeps one bit per
+// device ordinal (one static per kernel instantiation at the call site), so a process that drives
+// several GPUs, or several host threads, sets it exactly where it is missing.
 template <typename K>
-int allow_smem(K kernel, size_t bytes) {
+int allow_smem(K kernel, size_t bytes, std::atomic<uint64_t> &done) {
+  int dev = 0;
+  FA_CUDA_OK(cudaGetDevice(&dev));
+  const uint64_t bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return 0;
   FA_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  done.fetch_or(bit, std::memory_order_release);
   return 0;
 }
 
@@ -200,8 +208,8 @@ template <typename T, int DP, bool kAsync>
 int tiled_fwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
                      const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
   auto kern = fa::fa_tiled_fwd_kernel<T, DP, kAsync>;
-  static int once = allow_smem(kern, fa::t_fwd_smem<DP>());
-  if (once) return once;
+  static std::atomic<uint64_t> smem_ok{0};
+  if (int rc = allow_smem(kern, fa::t_fwd_smem<DP>(), smem_ok)) return rc;
   kern<<<dim3(tiles(p->Lq), (unsigned)(p->B * p->H)), fa::kTThreads, fa::t_fwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<T>(o), lse, gparams(p));
   return launched();
@@ -244,8 +252,9 @@ int tiled_bwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa
                      const fa_b200_tensor *dv, float *delta, cudaStream_t st) {
   auto kq = fa::fa_tiled_bwd_dq_kernel<T, DP, kAsync>;
   auto kkv = fa::fa_tiled_bwd_dkv_kernel<T, DP, kAsync>;
-  static int once = [&] { int rc = allow_smem(kq, fa::t_bwd_smem<DP>()); return rc ? rc : allow_smem(kkv, fa::t_bwd_smem<DP>()); }();
-  if (once) return once;
+  static std::atomic<uint64_t> smem_ok_q{0}, smem_ok_kv{0};
+  if (int rc = allow_smem(kq, fa::t_bwd_smem<DP>(), smem_ok_q)) return rc;
+  if (int rc = allow_smem(kkv, fa::t_bwd_smem<DP>(), smem_ok_kv)) return rc;
   const unsigned groups = (unsigned)(p->B * p->H);
   kq<<<dim3(tiles(p->Lq), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(o), view<const T>(dout), lse,
@@ -307,12 +316,8 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   fp.scale_log2 = p->softmax_scale * fa::kLog2e;
   fp.num_pairs = (p->Lq + 2 * fa::kBlockM - 1) / (2 * fa::kBlockM);
   auto kern = fa::fa_fwd_sm100_kernel<D, kBf16>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    FA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    fa::FwdSmem<D>::kAlloc));
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> smem_ok{0};  // per instantiation
+  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok)) return rc;
   const unsigned grid = (unsigned)((int64_t)p->B * p->H * fp.num_pairs);
 #ifdef FA_FWD_TRACE
   static unsigned long long *d_trace = nullptr;
@@ -384,12 +389,8 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   bp.num_kv_tiles = (p->Lk + 127) / 128;
   const bool gqa = bp.kv_ratio > 1;
   auto kern = gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false>;
-  static bool attr_set[2] = {false, false};
-  if (!attr_set[gqa]) {
-    FA_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    fa::BwdSmem<D>::kBytes));
-    attr_set[gqa] = true;
-  }
+  static std::atomic<uint64_t> smem_ok[2] = {{0}, {0}};
+  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa])) return rc;
   const unsigned grid = (unsigned)((int64_t)p->B * Hkv * bp.num_kv_tiles);  // one CTA per (batch, K/V head, KV tile)
 #ifdef FA_BWD_TRACE
   static unsigned long long *d_btrace = nullptr;
