@@ -256,6 +256,90 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar) {
       : "memory");
 }
 
+// ------------------------------------------------------------------ CTA pairs (cta_group::2) and clusters
+// Everything down to umma2_commit_mc is exercised by tests/cuda/umma2_probe.cu modes 0-3 (exact on
+// B200).  The distributed-shared-memory helpers after it are exercised by mode 4 of the same probe.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {  // every thread of every CTA of the cluster
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Issued by the SAME warp index in both CTAs of the pair; each CTA gets the address in its own smem.
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc2(uint32_t *smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {  // after a cluster barrier: both CTAs are done
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// Pair-wide products, issued by one thread of the LEADER CTA (cluster rank 0).  Descriptor offsets
+// and TMEM addresses are the same numbers in both CTAs.  M (in the instruction descriptor) is the
+// pair's: 256 = 128 rows per CTA on lanes 0-127; 128 = 64 rows per CTA (lane l < 64: columns
+// n < N/2, lane 64 + l: n >= N/2, both in columns [0, N/2)), at half the rate.  Each CTA supplies
+// half of B: rows [N/2 c, N/2 (c+1)) of a K-major B, or the N/2-column panel c of an MN-major B.
+__device__ __forceinline__ void umma2_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive, once the pair's earlier MMAs have completed, on the mbarrier at this shared-memory offset
+// in every CTA of `cta_mask` (3 = both)
+__device__ __forceinline__ void umma2_commit_mc(uint64_t *bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(smem_u32(bar)), "h"(cta_mask)
+      : "memory");
+}
+// shared::cta address -> the same offset in CTA `rank` of the cluster (a shared::cluster address)
+__device__ __forceinline__ uint32_t map_to_cta(const void *p, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t cluster_addr, uint4 v) {
+  asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+// release at cluster scope: the stores above (own or remote shared memory) are visible to whoever
+// acquires the barrier's phase in the other CTA
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t *bar, uint32_t parity) {  // acquire at cluster scope
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t.reg .b32 spins;\n\t"
+      "mov.b32 spins, 0;\n\t"
+      "LAB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "add.u32 spins, spins, 1;\n\t"
+      "setp.gt.u32 P1, spins, %2;\n\t"
+      "@P1 trap;\n\t"
+      "bra LAB_WAIT;\n\t"
+      "DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(parity), "n"(FA_MBAR_SPIN_LIMIT)
+      : "memory");
+}
+
 // ------------------------------------------------------------------ tcgen05.ld / st
 // 32x32b: thread t of the warp <-> TMEM lane (warp%4)*32 + t; N consecutive 32-bit columns.
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {

@@ -3,7 +3,7 @@
 # shared-memory store traffic (modes 10-14).  One process per mode: a trap kills only that mode.
 mkdir -p gpurun_out; L=gpurun_out/umma2.log; : > $L
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv,noheader >> $L
-for m in 0 1 2 3; do
+for m in 0 1 2 3 4; do
   echo "=== mode $m" >> $L
   timeout 60 build/umma2_probe $m >> $L 2>&1; echo "exit $?" >> $L
 done

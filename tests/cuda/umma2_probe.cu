@@ -12,6 +12,10 @@
 //   2: M=128  D[128x128] = A[128 x K=128] * B[128 x K]^T       SS K/K, 64 rows of D per CTA
 //   3: M=128  D = At[K=128 x 128]^T * Bt[K x 128]              SS, A MN-major (64 columns of At per
 //                                                              CTA), B MN-major split by N (dQ = dS K)
+//   4: distributed shared memory: each CTA of the pair writes 16 KB into the OTHER CTA's shared memory
+//      (st.shared::cluster.v4) and arrives on the other CTA's mbarrier (release.cluster, one arrival
+//      per warp); the receiver waits (acquire.cluster), verifies, and hands the buffer back the same
+//      way.  64 rounds: exactness + bytes/clk per direction (the dS^T exchange of a pair backward)
 //   10+: issue-rate modes, all SMs busy: clk per tcgen05.mma with `traffic` 16-byte shared-memory
 //        stores per thread per loop turn from 4 bystander warps (models TMA writes / drain staging)
 //        umma2_probe 10 <traffic>   cta_group::1 SS 128x128x16   (today's kernels)
@@ -30,40 +34,7 @@ using namespace fa;
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(2); } } while (0)
 
-// ------------------------------------------------------------------ cta_group::2 wrappers
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-template <int kCols>
-__device__ __forceinline__ void tmem_alloc2(uint32_t *smem_dst) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "n"(kCols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-template <int kCols>
-__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
-}
-__device__ __forceinline__ void umma2_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-               "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-               ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ void umma2_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-               "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-               ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
-}
-// arrive on the mbarrier at the same shared-memory offset in every CTA of `mask`
-__device__ __forceinline__ void umma2_commit_mc(uint64_t *bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
-}
+// (the cta_group::2 / cluster wrappers live in csrc/sm100_ptx.cuh)
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                   const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
@@ -171,6 +142,41 @@ probe2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
   }
   tc_fence_before(); __syncthreads(); cluster_sync_all();
   if (warp == 1) tmem_dealloc2<256>(tb);
+}
+
+// ------------------------------------------------------------------ mode 4: DSMEM exchange
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+dsmem_probe_kernel(int rounds, int *bad_out, long long *clk_out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t *full = (uint64_t *)(smem + 16384);   // the peer's 8 warps arrive: its data is in my buffer
+  uint64_t *empty = full + 1;                     // the peer's 8 warps arrive: it has read its buffer (my data)
+  const uint32_t rank = cluster_ctarank(), peer = rank ^ 1;
+  if (threadIdx.x == 0) { mbar_init(full, 8); mbar_init(empty, 8); fence_barrier_init(); }
+  __syncthreads(); cluster_sync_all();
+  const uint32_t peer_buf = map_to_cta(smem, peer), peer_full = map_to_cta(full, peer), peer_empty = map_to_cta(empty, peer);
+  int bad = 0;
+  const long long t0 = clock64();
+  for (int r = 0; r < rounds; ++r) {
+    if (r > 0) mbar_wait_cluster(empty, (r - 1) & 1);
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t idx = c * 256 + threadIdx.x;  // 16-byte chunk index, consecutive threads -> consecutive chunks
+      st_cluster_v4(peer_buf + idx * 16, make_uint4(idx, rank, (uint32_t)r, idx ^ 0x5a5a5a5au));
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(peer_full);
+    mbar_wait_cluster(full, r & 1);
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t idx = c * 256 + threadIdx.x;
+      const uint4 v = *(const uint4 *)(smem + idx * 16);
+      if (v.x != idx || v.y != peer || v.z != (uint32_t)r || v.w != (idx ^ 0x5a5a5a5au)) ++bad;
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(peer_empty);
+  }
+  const long long t1 = clock64();
+  if (bad) atomicAdd(bad_out, bad);
+  if (threadIdx.x == 0) clk_out[rank] = t1 - t0;
+  cluster_sync_all();  // no CTA may exit while the peer can still write into it
 }
 
 // ------------------------------------------------------------------ issue-rate kernel
@@ -327,6 +333,20 @@ int main(int argc, char **argv) {
     if (mode == 13) run_rate<2, 256, true>("cg2 TS 256x128x16", traffic);
     if (mode == 14) run_rate<1, 128, true>("cg1 TS 128x128x16", traffic);
     return 0;
+  }
+  if (mode == 4) {
+    const int rounds = 64;
+    int *bad; long long *clk;
+    CK(cudaMalloc(&bad, 4)); CK(cudaMalloc(&clk, 16)); CK(cudaMemset(bad, 0, 4)); CK(cudaMemset(clk, 0, 16));
+    CK(cudaFuncSetAttribute(dsmem_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 17 * 1024));
+    dsmem_probe_kernel<<<2, 256, 17 * 1024>>>(rounds, bad, clk);
+    CK(cudaDeviceSynchronize());
+    int hb; long long hc[2];
+    CK(cudaMemcpy(&hb, bad, 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(hc, clk, 16, cudaMemcpyDeviceToHost));
+    printf("probe2 mode 4 (DSMEM 16 KB each way x %d rounds, remote mbarrier hand-off): %s (%d bad chunks); "
+           "%.0f clk per round = %.1f B/clk per direction incl. verification\n",
+           rounds, hb ? "FAIL" : "PASS", hb, (double)hc[0] / rounds, 16384.0 * rounds / (double)hc[0]);
+    return hb ? 1 : 0;
   }
   // 1. coded run: where does D[m][n] land?
   Problem pc = make_problem(mode, true);
