@@ -60,7 +60,17 @@ constexpr bool kDrainSingle = FA_BWD_DRAIN_SINGLE != 0;
 #ifndef FA_BWD_DRAIN_PIPE
 #define FA_BWD_DRAIN_PIPE 0
 #endif
-constexpr bool kDrainPipe = FA_BWD_DRAIN_PIPE != 0;  // one 4 KB staging slab per drain warp instead of two  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
+constexpr bool kDrainPipe = FA_BWD_DRAIN_PIPE != 0;
+// FA_BWD_DRAIN_REGS: a drain warp reads ALL of its dQ columns into registers at once and releases
+// TMEM (dq_empty) before it touches the staging slabs, so dP^T of the next Q tile never waits for
+// the reduce engine.  Costs 152 registers per drain thread instead of 104; the compute warps give
+// them up (168 -> 144), which they can afford once the row statistics no longer live in registers
+// (FA_BWD_STATS_MMA).  Untimed: written after the round's GPU budget ended.
+#ifndef FA_BWD_DRAIN_REGS
+#define FA_BWD_DRAIN_REGS 0
+#endif
+constexpr bool kDrainRegs = FA_BWD_DRAIN_REGS != 0;
+constexpr int kBwdRegCompute = kDrainRegs ? 144 : 168, kBwdRegDrain = kDrainRegs ? 152 : 104;  // one 4 KB staging slab per drain warp instead of two  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
 
 struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
@@ -393,7 +403,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // Each warp drains its own 32 query rows independently: TMEM -> registers -> a private
     // 2 x 4 KB staging ring -> TMA reduce-add (32-row boxes).  No cross-warp barriers, and one
     // reduce is in flight while the next slab is being staged.
-    reg_dealloc<104>();
+    if (kDrainRegs) reg_alloc<kBwdRegDrain>(); else reg_dealloc<kBwdRegDrain>();
     const int w = warp & 3;
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
     uint8_t *wstage = smem + L::kDQOff + w * (L::kDrainSlabs * 4096);
@@ -406,7 +416,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (blockIdx.x == 0 && w == 0 && lane == 0) p.trace[10] += clock64() - tf0;  // drain warp idle: waiting for dQ
 #endif
       tc_fence_after();
-      if (kDrainSingle) {
+      if (kDrainSingle && !kDrainRegs) {
         // One 4 KB slab (32 fp32 columns) per warp: a round = wait until the previous reduce has
         // read the slab, store 32 columns, reduce.  Two rounds of columns are held in registers, so
         // dQ has left TMEM (dq_empty) once the slabs of rounds 0 .. D/32-3 are on their way.
@@ -440,6 +450,33 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             tma_store_commit();
           }
 #endif
+        }
+        continue;
+      }
+      if (kDrainRegs) {
+        constexpr int kSlabs = D / 32;
+        uint32_t r[kSlabs][32];
+        #pragma unroll
+        for (int k = 0; k < kSlabs; ++k) tmem_ld32(tDQ + k * 32, r[k]);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive_warp(dq_empty);  // dQ has left TMEM: nothing below is on the tensor pipe's path
+        #pragma unroll
+        for (int k = 0; k < kSlabs; ++k) {
+          uint8_t *slab = wstage + (k % L::kDrainSlabs) * 4096;
+          if (lane == 0) tma_store_wait_read<L::kDrainSlabs - 1>();  // the reduce that last used this slab has read it
+          __syncwarp();
+          #pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 v4 = make_uint4(r[k][c * 4], r[k][c * 4 + 1], r[k][c * 4 + 2], r[k][c * 4 + 3]);
+            *reinterpret_cast<uint4 *>(slab + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_reduce_add_4d(&tmDQ, slab, k * 32, i * 128 + w * 32, h, b);
+            tma_store_commit();
+          }
         }
         continue;
       }
@@ -533,7 +570,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (lane == 0) tma_store_wait<0>();
   } else if (warp < 8) {
     // ============================== compute: P^T, dS^T ; epilogue dK, dV ==============================
-    reg_alloc<168>();
+    reg_alloc<kBwdRegCompute>();
     const int wg = warp >> 2;                      // which 64 query columns of the tile
     const int row = (warp & 3) * 32 + lane;        // key row within the KV tile (= TMEM lane)
     const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
