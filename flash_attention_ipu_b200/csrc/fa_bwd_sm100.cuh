@@ -23,6 +23,14 @@
 //   warps 0-7  : compute (2 warpgroups; thread <-> key row; WG w owns query columns [64w,64w+64))
 //   warps 8-11 : dQ drain (TMEM -> regs -> smem -> TMA reduce-add)
 //   warp 12 TMA producer | warp 13 MMA issuer | warp 14 TMEM alloc | warp 15 idle
+//
+// Build switches (all default off; the default build is the measured v6/v7 kernel.  DESIGN.md 4.6):
+//   FA_BWD_DK_TS         dS^T also in TMEM, dK as a TS product           correct, +4.9 % cycles
+//   FA_BWD_DRAIN_SINGLE  one 4 KB staging slab per drain warp            correct, +6.9 %
+//   FA_BWD_STATS_MMA     -lse / -delta added by the tensor core          correct, no gain (implies DRAIN_SINGLE)
+//   FA_BWD_DRAIN_PIPE    one slab per bulk group, wait_group.read 1      parity cases green, not yet timed
+//   FA_BWD_DRAIN_REGS    all dQ columns in registers, TMEM released first  compiled only (written without a GPU)
+//   FA_EXPERIMENT_*      timing experiments that remove work (wrong results), FA_BWD_TRACE: wait timers
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
