@@ -138,9 +138,10 @@ void tmap_insert(const TmapKey &k, const CUtensorMap &m) {
 }
 
 // (B,H,L,D) tensor, box = 128 bytes of D x `box_rows` rows, 128B swizzle.
+// `box_bytes` = 64: 64 bytes of D per box row, 64B swizzle (the 2 KB dQ staging slabs).
 int make_tmap(CUtensorMap *m, const fa_b200_tensor *t, int dtype, int B, int H, int L, int D,
-              int box_rows) {
-  const TmapKey key{t->ptr, t->stride_b, t->stride_h, t->stride_l, dtype, B, H, L, D, box_rows};
+              int box_rows, int box_bytes = 128) {
+  const TmapKey key{t->ptr, t->stride_b, t->stride_h, t->stride_l, dtype, B, H, L, D, box_rows | (box_bytes << 16)};
   if (tmap_lookup(key, m)) {
     g_tmap_hits.fetch_add(1, std::memory_order_relaxed);
     return 0;
@@ -158,10 +159,11 @@ int make_tmap(CUtensorMap *m, const fa_b200_tensor *t, int dtype, int B, int H, 
   if (H == 1 && (sh == 0 || sh % 16)) sh = sl * L;
   if (B == 1 && (sb == 0 || sb % 16)) sb = sh * H;
   cuuint64_t strides[3] = {sl, sh, sb};
-  cuuint32_t box[4] = {(cuuint32_t)(128 / es), (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t box[4] = {(cuuint32_t)(box_bytes / es), (cuuint32_t)box_rows, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, dt, 4, t->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  box_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(FA_B200_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   tmap_insert(key, *m);
@@ -376,11 +378,11 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tk, k, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tv, v, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdo, dout, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
-  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32)) return rc;
+  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32, fa::BwdSmem<D>::kSlabCols * 4)) return rc;
   if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
-  bp.lse2 = lse2; bp.delta = delta;
+  bp.lse2 = lse2; bp.delta = delta; bp.dq_acc = dq_acc;
   bp.slab_delta = ws; bp.slab_lse = ws + ws_stat_bytes(p);
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
   bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;
@@ -409,6 +411,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
             (double)h[0] / h[6], (double)h[1] / h[6], (double)h[2] / h[6], (double)h[3] / h[6], (double)h[4] / h[6], (double)h[5] / h[6], h[6]);
     fprintf(stderr, "bwd trace (CTA 0, drain warp 0, clk per iteration): wait dq_full %.0f | dq_full->dq_empty %.0f | wait_read before half 0 %.0f, before half 1 %.0f\n",
             (double)h[10] / h[6], (double)h[11] / h[6], (double)h[8] / h[6], (double)h[9] / h[6]);
+    fprintf(stderr, "bwd trace (CTA 0): prologue (entry -> first S issued) %llu clk, epilogue (loop end -> exit) %llu clk\n", h[12], h[14]);
   }
 #endif
   // dQ = softmax_scale * dq_acc, cast to the output dtype

@@ -78,6 +78,9 @@ constexpr bool kDrainPipe = FA_BWD_DRAIN_PIPE != 0;
 #define FA_BWD_DRAIN_REGS 0
 #endif
 constexpr bool kDrainRegs = FA_BWD_DRAIN_REGS != 0;
+#ifndef FA_BWD_RED_COLS
+#define FA_BWD_RED_COLS 0
+#endif
 constexpr int kBwdRegCompute = kDrainRegs ? 144 : 168, kBwdRegDrain = kDrainRegs ? 152 : 104;  // one 4 KB staging slab per drain warp instead of two  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
 
 struct BwdParams {
@@ -86,6 +89,7 @@ struct BwdParams {
   // FA_BWD_STATS_MMA: the same two statistics as ready-made shared-memory images, one 4 KB slab per
   // 128-row Q tile ([G][Lq_pad / 128][4096] bytes each; see fa_bwd_prep_kernel)
   const uint8_t *slab_lse, *slab_delta;
+  float *dq_acc;       // [G][Lq][D] fp32 dQ accumulator (FA_BWD_DRAIN_RED addresses it directly)
   int Lq, Lk, H, Lq_pad;
   int Hkv, kv_ratio;   // K/V heads and query heads per K/V head (H = Hkv * kv_ratio; 1 = multi-head)
   int causal, shift;
@@ -106,8 +110,16 @@ struct BwdSmem {
   static constexpr int kDOOff = kQOff + 2 * kTileBytes;       // 1 stage
   static constexpr int kDSOff = kDOOff + kTileBytes;          // dS^T [128 keys][128 q] bf16
   static constexpr int kDQOff = kDSOff + 2 * kHalfBytes;      // fp32 staging: 4 drain warps x kDrainSlabs x 4 KB
-  static constexpr int kDrainSlabs = kDrainSingle ? 1 : 2;
-  static constexpr int kStatOff = kDQOff + 4 * kDrainSlabs * 4096;
+  // FA_BWD_SLAB2K (with FA_BWD_DRAIN_REGS): the staging ring of a drain warp is two slabs of 32 rows x
+  // 16 fp32 columns (2 KB, 64-byte rows, SWIZZLE_64B) instead of 32 columns -- 16 KB for the four
+  // warps, which leaves room for the statistic operand slabs of FA_BWD_STATS_MMA
+#ifdef FA_BWD_SLAB2K
+  static constexpr int kSlabCols = 16, kDrainSlabs = 2;
+#else
+  static constexpr int kSlabCols = 32, kDrainSlabs = kDrainSingle ? 1 : 2;
+#endif
+  static constexpr int kSlabBytes = 32 * kSlabCols * 4;
+  static constexpr int kStatOff = kDQOff + 4 * kDrainSlabs * kSlabBytes;
   // !kStatsMma: 2 stages x (lse2[128] | delta[128]) fp32.   kStatsMma: four 4 KB no-swizzle K-major
   // [128 x 16] operand slabs: lse (stage 0, 1; travel with Q), delta (travels with dO), ones
   static constexpr int kSlabLseOff = kStatOff, kSlabDeltaOff = kStatOff + 2 * 4096, kSlabOnesOff = kStatOff + 3 * 4096;
@@ -166,6 +178,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
+#ifdef FA_BWD_TRACE
+  const long long t_entry = clock64();
+#endif
   const int gk = blockIdx.x / p.num_kv_tiles;  // (batch, K/V head)
   const int j = blockIdx.x % p.num_kv_tiles;   // ascending: the KV tiles with most Q tiles first
   const int b = gk / p.Hkv, hk = gk % p.Hkv;
@@ -307,6 +322,24 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       // and dV(it+1) is what runs while the drain empties dQ(it).
       for (int it = 0; it < n; ++it) {
         const uint32_t q_stage = (it & 1) * kTile16;
+#ifdef FA_BWD_ORDER2  // dP(it) dV(it) S(it+1) dK(it) dQ(it): dS^T gets dV + S as cover, dP(it+1) waits for the (short) drain
+        FA_BT_WAIT(0, mbar_wait(do_full, it & 1));
+        if (it > 0) FA_BT_WAIT(1, mbar_wait(dq_empty, (it - 1) & 1));
+        tc_fence_after();
+        if (leader) {
+          issue_kk(tDP, v_kmaj, do_kmaj, delta_ns);
+          umma_commit(dp_full);
+        }
+        FA_BT_WAIT(2, mbar_wait(p_full, it & 1));
+        tc_fence_after();
+        if (leader) {
+          #pragma unroll
+          for (int k = 0; k < 8; ++k)
+            umma_ts2(tDV, tS + (k < 4 ? 8 * k : 64 + 8 * (k - 4)), do_mn + k * (2048 >> 4), hi, idesc_dv,
+                     (it > 0 || k > 0));
+          umma_commit(do_empty);
+        }
+#else
         FA_BT_WAIT(2, mbar_wait(p_full, it & 1));
         FA_BT_WAIT(0, mbar_wait(do_full, it & 1));
         tc_fence_after();
@@ -323,6 +356,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           umma_commit(dp_full);
           umma_commit(do_empty);
         }
+#endif
         if (it + 1 < n) {
           FA_BT_WAIT(3, mbar_wait(&q_full[(it + 1) & 1], ((it + 1) >> 1) & 1));
           tc_fence_after();
@@ -402,6 +436,8 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int t = 0; t < 5; ++t) p.trace[t] = tr[t];
         p.trace[5] = clock64() - t_loop;
         p.trace[6] = n;
+        p.trace[12] = t_loop - t_entry;  // CTA entry -> first S^T issued (prologue)
+        p.trace[13] = clock64();         // loop end (absolute; the CTA-exit stamp subtracts it)
       }
 #endif
       (void)kHalf16;
@@ -414,7 +450,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     if (kDrainRegs) reg_alloc<kBwdRegDrain>(); else reg_dealloc<kBwdRegDrain>();
     const int w = warp & 3;
     const uint32_t tDQ = tmem_base + kColDP + (static_cast<uint32_t>(w * 32) << 16);
-    uint8_t *wstage = smem + L::kDQOff + w * (L::kDrainSlabs * 4096);
+    uint8_t *wstage = smem + L::kDQOff + w * (L::kDrainSlabs * L::kSlabBytes);
     for (int it = 0, h = h0, i = i0; it < n; ++it, bwd_next_tile<kGqa>(h, i, i0, num_q_tiles)) {
 #ifdef FA_BWD_TRACE
       const long long tf0 = clock64();
@@ -463,30 +499,104 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       if (kDrainRegs) {
         constexpr int kSlabs = D / 32;
+#ifdef FA_BWD_TRACE
+        const bool tr_on = blockIdx.x == 0 && w == 0 && lane == 0;
+        const long long tq0 = clock64();
+#endif
+#ifdef FA_BWD_DRAIN_RED
+        // dQ leaves the SM as red.global.add.v2.f32 straight from registers: the 16x256b TMEM load
+        // shape gives lanes 4r .. 4r+3 eight consecutive fp32 of row r (and of row r + 8), so one
+        // warp instruction adds 8 whole 32-byte sectors.  No staging, no TMA.
+        uint32_t r[2][64];
+        tmem_ld_16x256b_x16(tDQ, r[0]);
+        tmem_ld_16x256b_x16(tDQ + (16u << 16), r[1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive_warp(dq_empty);
+#ifdef FA_BWD_TRACE
+        if (tr_on) p.trace[11] += clock64() - tq0;
+#endif
+        {
+          const int q_row0 = i * 128 + w * 32;
+          float *base = p.dq_acc + (static_cast<size_t>(b * p.H + h) * p.Lq + q_row0) * D + 2 * (lane & 3);
+          #pragma unroll
+          for (int hf = 0; hf < 2; ++hf)
+            #pragma unroll
+            for (int sub = 0; sub < 2; ++sub) {
+              const int row = hf * 16 + sub * 8 + (lane >> 2);
+              if (q_row0 + row < p.Lq) {
+                float *rp = base + static_cast<size_t>(row) * D;
+                #pragma unroll
+                for (int c = 0; c < 16; ++c)
+                  red_add_v2(rp + c * 8, r[hf][c * 4 + sub * 2], r[hf][c * 4 + sub * 2 + 1]);
+              }
+            }
+        }
+        continue;
+#else
         uint32_t r[kSlabs][32];
         #pragma unroll
         for (int k = 0; k < kSlabs; ++k) tmem_ld32(tDQ + k * 32, r[k]);
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive_warp(dq_empty);  // dQ has left TMEM: nothing below is on the tensor pipe's path
+#ifdef FA_BWD_TRACE
+        if (tr_on) p.trace[11] += clock64() - tq0;
+#endif
+        // FA_BWD_RED_COLS: the last kRedCols columns of the tile leave as red.global.add.v4.f32 straight
+        // from the registers (LSU path) while the rest goes through staging + TMA reduce-add: the TMA
+        // unit moves reduce-adds at 25.4 B/clk/SM (tests/cuda/smem_contention.cu) and is the unit that
+        // paces the loop, so part of the volume takes the other road into L2.
+        constexpr int kRedCols = FA_BWD_RED_COLS;
+        if (kRedCols > 0) {
+          const int qrow = i * 128 + w * 32 + lane;
+          if (qrow < p.Lq) {
+            float *rp = p.dq_acc + (static_cast<size_t>(b * p.H + h) * p.Lq + qrow) * D + (D - kRedCols);
+            #pragma unroll
+            for (int c = 0; c < kRedCols; c += 4) {
+              const int col = D - kRedCols + c;
+              red_add_v4(rp + c, r[col >> 5][col & 31], r[col >> 5][(col & 31) + 1], r[col >> 5][(col & 31) + 2],
+                         r[col >> 5][(col & 31) + 3]);
+            }
+          }
+        }
+        constexpr int kOps = (D - kRedCols) / L::kSlabCols;  // TMA reduce-adds per warp per Q tile
+        constexpr int kChunks = L::kSlabCols / 4;        // 16-byte chunks per staged row
         #pragma unroll
-        for (int k = 0; k < kSlabs; ++k) {
-          uint8_t *slab = wstage + (k % L::kDrainSlabs) * 4096;
+        for (int k = 0; k < kOps; ++k) {
+          uint8_t *slab = wstage + (k % L::kDrainSlabs) * L::kSlabBytes;
+#ifdef FA_BWD_TRACE
+          const long long tw0 = clock64();
+#endif
           if (lane == 0) tma_store_wait_read<L::kDrainSlabs - 1>();  // the reduce that last used this slab has read it
+#ifdef FA_BWD_TRACE
+          if (tr_on) p.trace[8] += clock64() - tw0;
+#endif
           __syncwarp();
           #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            uint4 v4 = make_uint4(r[k][c * 4], r[k][c * 4 + 1], r[k][c * 4 + 2], r[k][c * 4 + 3]);
-            *reinterpret_cast<uint4 *>(slab + lane * 128 + ((c ^ (lane & 7)) * 16)) = v4;
+          for (int c = 0; c < kChunks; ++c) {
+            const int col = k * L::kSlabCols + c * 4;
+            uint4 v4 = make_uint4(r[col >> 5][col & 31], r[col >> 5][(col & 31) + 1], r[col >> 5][(col & 31) + 2],
+                                  r[col >> 5][(col & 31) + 3]);
+            // SWIZZLE_128B: chunk ^= row % 8 (128-byte rows); SWIZZLE_64B: chunk ^= (row / 2) % 4 (64-byte rows)
+            const int pc = kChunks == 8 ? (c ^ (lane & 7)) : (c ^ ((lane >> 1) & 3));
+            *reinterpret_cast<uint4 *>(slab + lane * (L::kSlabCols * 4) + pc * 16) = v4;
           }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_reduce_add_4d(&tmDQ, slab, k * 32, i * 128 + w * 32, h, b);
+#if defined(FA_EXPERIMENT_DRAIN_STORE)     // timing experiment only (wrong results): plain TMA store, no L2 reduction
+            tma_store_4d(&tmDQ, slab, k * L::kSlabCols, i * 128 + w * 32, h, b);
+#elif defined(FA_EXPERIMENT_DRAIN_SAMETILE)  // timing experiment only (wrong results): every Q tile reduces into tile i0
+            tma_reduce_add_4d(&tmDQ, slab, k * L::kSlabCols, i0 * 128 + w * 32, h, b);
+#else
+            tma_reduce_add_4d(&tmDQ, slab, k * L::kSlabCols, i * 128 + w * 32, h, b);
+#endif
             tma_store_commit();
           }
         }
         continue;
+#endif
       }
       if (kDrainPipe) {
         constexpr int kSlabs = D / 32;
@@ -575,7 +685,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #endif
       }
     }
-    if (lane == 0) tma_store_wait<0>();
+    // the staging slabs must stay valid until the last reduce has READ them; completion of the
+    // writes themselves is guaranteed by the kernel boundary (the convert pass is a later launch)
+    if (lane == 0) tma_store_wait_read<0>();
   } else if (warp < 8) {
     // ============================== compute: P^T, dS^T ; epilogue dK, dV ==============================
     reg_alloc<kBwdRegCompute>();
@@ -597,7 +709,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_wait(&q_full[it & 1], (it >> 1) & 1);   // makes the lse2 / delta stage visible to this thread
         #pragma unroll
         for (int c4 = 0; c4 < (kStatsMma ? 0 : 16); ++c4) {
+#ifdef FA_EXPERIMENT_NO_STATS  // timing experiment only (wrong results): no broadcast loads of the row statistics
+          const float4 l4 = make_float4(-3.f, -3.f, -3.f, -3.f); (void)stat;
+#else
           const float4 l4 = stat[c4];
+#endif
           nl[4 * c4] = l4.x; nl[4 * c4 + 1] = l4.y; nl[4 * c4 + 2] = l4.z; nl[4 * c4 + 3] = l4.w;
         }
       }
@@ -640,6 +756,14 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int c = 0; c < 64; ++c)
           if (c < cmin) pr[c] = 0.f;
       }
+      // key rows past the end of K (last KV tile of a ragged Lk): K is zero-filled there, so
+      // S = 0 and exp2(-lse2) is unbounded for rows with a strongly negative LSE.  Select, not
+      // multiply: the value may be inf / polynomial garbage.  (The forward masks the same keys
+      // through `limit = Lk - 1 - col0`.)
+      if (j * 128 + 128 > p.Lk && key >= p.Lk) {
+        #pragma unroll
+        for (int c = 0; c < 64; ++c) pr[c] = 0.f;
+      }
       {
         uint32_t pk[32];
         #pragma unroll
@@ -654,7 +778,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       float nd[kStatsMma ? 2 : 32];
       #pragma unroll
       for (int c4 = 0; c4 < (kStatsMma ? 0 : 8); ++c4) {
+#ifdef FA_EXPERIMENT_NO_STATS
+        const float4 d4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#else
         const float4 d4 = stat[32 + c4];
+#endif
         nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
       }
       mbar_wait(dp_full, it & 1);
@@ -679,7 +807,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (hf == 0 && !kStatsMma) {
           #pragma unroll
           for (int c4 = 0; c4 < (kStatsMma ? 0 : 8); ++c4) {
+#ifdef FA_EXPERIMENT_NO_STATS
+            const float4 d4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#else
             const float4 d4 = stat[40 + c4];
+#endif
             nd[4 * c4] = d4.x; nd[4 * c4 + 1] = d4.y; nd[4 * c4 + 2] = d4.z; nd[4 * c4 + 3] = d4.w;
           }
         }
@@ -743,7 +875,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tma_store_4d(&tmDV, smem + L::kQOff + L::kTileBytes + hh * L::kHalfBytes, hh * 64, j * 128, hk, b);
       }
       tma_store_commit();
-      tma_store_wait<0>();
+      tma_store_wait_read<0>();
     }
   } else {
     reg_dealloc<72>();
@@ -751,6 +883,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+#ifdef FA_BWD_TRACE
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.trace[14] = clock64() - p.trace[13];  // MMA loop end -> CTA exit (epilogue)
+#endif
   if (warp == 14) tmem_dealloc<512>(tmem_base);
 }
 
