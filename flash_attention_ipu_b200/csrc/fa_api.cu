@@ -347,10 +347,22 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
 // ---------------------------------------------------------------- tensor family: backward
 size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 int lq_pad(const fa_b200_problem *p) { return (p->Lq + 127) / 128 * 128; }
-// workspace: delta[G][Lq_pad] | lse2[G][Lq_pad] | dq_acc[G][Lq][D] (fp32), each 256-byte aligned
-// (FA_BWD_STATS_MMA: the two statistics are 32-byte operand-slab rows instead of one float each)
+// workspace: delta[G][Lq_pad] | lse2[G][Lq_pad] | dq_acc[G][Lq][D] (fp32) | work counter, each 256-byte aligned
 size_t ws_stat_bytes(const fa_b200_problem *p) {
-  return align256((size_t)p->B * p->H * lq_pad(p) * (fa::kStatsMma ? 32 : sizeof(float)));
+  return align256((size_t)p->B * p->H * lq_pad(p) * sizeof(float));
+}
+size_t ws_acc_bytes(const fa_b200_problem *p) { return align256((size_t)p->B * p->H * p->Lq * p->D * sizeof(float)); }
+
+int sm_count() {  // per device: a process may drive several GPUs
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  int n = cached[dev & 63].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev & 63].store(n, std::memory_order_relaxed);
+  }
+  return n;
 }
 
 template <int D, bool kBf16>
@@ -363,12 +375,12 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   float *delta = reinterpret_cast<float *>(ws);
   float *lse2 = reinterpret_cast<float *>(ws + ws_stat_bytes(p));
   float *dq_acc = reinterpret_cast<float *>(ws + 2 * ws_stat_bytes(p));
+  int *counter = reinterpret_cast<int *>(ws + 2 * ws_stat_bytes(p) + ws_acc_bytes(p));
   const int G = p->B * p->H, Lp = lq_pad(p);
   fa::fa_bwd_prep_kernel<T, D><<<blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st>>>(
       reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
       reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
-      delta, lse2, dq_acc, p->B, p->H, p->Lq, Lp, /*slab_lse=*/ws + ws_stat_bytes(p), /*slab_delta=*/ws,
-      1.f / p->softmax_scale);
+      delta, lse2, dq_acc, p->B, p->H, p->Lq, Lp, counter);
   if (int rc = launched()) return rc;
 
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
@@ -378,22 +390,25 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tk, k, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tv, v, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdo, dout, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
-  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32, fa::BwdSmem<D>::kSlabCols * 4)) return rc;
+  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32)) return rc;
   if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
-  bp.lse2 = lse2; bp.delta = delta; bp.dq_acc = dq_acc;
-  bp.slab_delta = ws; bp.slab_lse = ws + ws_stat_bytes(p);
+  bp.lse2 = lse2; bp.delta = delta; bp.sched_counter = counter;
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
   bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;
   bp.causal = p->causal; bp.shift = p->q_pos0 - p->kv_pos0;
   bp.scale = p->softmax_scale; bp.scale_log2 = p->softmax_scale * fa::kLog2e;
   bp.num_kv_tiles = (p->Lk + 127) / 128;
+  const int64_t items = (int64_t)p->B * Hkv * bp.num_kv_tiles;  // one work item per (batch, K/V head, KV tile)
+  if (items > INT32_MAX) return fail(FA_B200_ERR_UNSUPPORTED, "too many KV tiles (%lld)", (long long)items);
+  bp.num_items = (int)items;
   const bool gqa = bp.kv_ratio > 1;
   auto kern = gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false>;
   static std::atomic<uint64_t> smem_ok[2] = {{0}, {0}};
   if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa])) return rc;
-  const unsigned grid = (unsigned)((int64_t)p->B * Hkv * bp.num_kv_tiles);  // one CTA per (batch, K/V head, KV tile)
+  // persistent: one CTA per SM (the kernel takes all of an SM's shared memory), items by atomic counter
+  const unsigned grid = (unsigned)(items < sm_count() ? items : sm_count());
 #ifdef FA_BWD_TRACE
   static unsigned long long *d_btrace = nullptr;
   if (!d_btrace) { cudaMalloc(&d_btrace, 16 * 8); }
@@ -407,11 +422,9 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
     unsigned long long h[16];
     cudaStreamSynchronize(st);
     cudaMemcpy(h, d_btrace, sizeof(h), cudaMemcpyDeviceToHost);
-    fprintf(stderr, "bwd trace (CTA 0, MMA warp, clk per iteration): do_full %.0f dq_empty %.0f p_full %.0f q_full %.0f ds_full %.0f | loop %.0f (n=%llu)\n",
-            (double)h[0] / h[6], (double)h[1] / h[6], (double)h[2] / h[6], (double)h[3] / h[6], (double)h[4] / h[6], (double)h[5] / h[6], h[6]);
-    fprintf(stderr, "bwd trace (CTA 0, drain warp 0, clk per iteration): wait dq_full %.0f | dq_full->dq_empty %.0f | wait_read before half 0 %.0f, before half 1 %.0f\n",
-            (double)h[10] / h[6], (double)h[11] / h[6], (double)h[8] / h[6], (double)h[9] / h[6]);
-    fprintf(stderr, "bwd trace (CTA 0): prologue (entry -> first S issued) %llu clk, epilogue (loop end -> exit) %llu clk\n", h[12], h[14]);
+    const double n = (double)(h[6] ? h[6] : 1);
+    fprintf(stderr, "bwd trace (CTA 0, MMA warp, clk per Q tile): do_full %.0f dq_empty %.0f p_full %.0f q_full %.0f ds_full %.0f | in-item loop %.0f | %llu tiles in %llu items, %.0f clk between items\n",
+            h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6], h[7], (double)h[8] / (h[7] ? h[7] : 1));
   }
 #endif
   // dQ = softmax_scale * dq_acc, cast to the output dtype
@@ -470,7 +483,7 @@ int fa_b200_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p) {
   if (!p || p->B <= 0 || p->H <= 0 || p->Lq <= 0 || p->D <= 0) return 0;
   if (family(p) == 1)
-    return 2 * ws_stat_bytes(p) + align256((size_t)p->B * p->H * p->Lq * p->D * sizeof(float));
+    return 2 * ws_stat_bytes(p) + ws_acc_bytes(p) + 256;
   return align256((size_t)p->B * p->H * p->Lq * sizeof(float));  // delta[G][Lq]
 }
 

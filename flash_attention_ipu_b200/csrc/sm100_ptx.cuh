@@ -127,6 +127,12 @@ __device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap *m, const vo
       "r"(c3)
       : "memory");
 }
+// pull one box of a tiled tensor into L2 (no shared-memory destination, no completion to wait for)
+__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap *m, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 // 1-D bulk copy global -> shared (16-byte aligned, size multiple of 16), completes on an mbarrier
 __device__ __forceinline__ void bulk_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
   asm volatile(

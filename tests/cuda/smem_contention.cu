@@ -6,6 +6,8 @@
 //   kind 0 none | 1 STS.128 | 2 LDS.128 (conflict-free) | 3 LDS.128 (all lanes one address: broadcast)
 //        4 bulk store smem->global (TMA reads smem)   | 5 bulk reduce-add.f32 smem->global
 //        6 bulk load global->smem (TMA writes smem)   | 7 tcgen05.ld 32x32b.x32 (TMEM reads)
+//        8 warps 1-2 bulk reduce-add, warps 3-4 bulk load (do loads queue behind stores in the TMA unit?)
+//        9 warps 1-2 idle,            warps 3-4 bulk load (the reference for 8)
 // Global targets are 64 KB per SM (L2 resident).  Behind DESIGN.md section 4.6 (round 2).
 #include <cstdio>
 #include <cstdlib>
@@ -69,6 +71,9 @@ contention_kernel(int n_mma, int kind, int gap, float *gbuf, long long *clk_out,
       *stop = 1;
     }
   } else if (warp <= 4 && kind > 0) {
+    const int mix = kind;
+    if (kind == 8) kind = warp <= 2 ? 5 : 6;
+    if (kind == 9) kind = warp <= 2 ? 0 : 6;
     uint8_t *area = smem + 65536 + (warp - 1) * 16384;
     const long long t0 = clock64();
     long long ops = 0, next = t0;
@@ -110,9 +115,10 @@ contention_kernel(int n_mma, int kind, int gap, float *gbuf, long long *clk_out,
         acc += r[0] + r[31];
       }
       ++ops;
+      if (kind == 0) break;
     }
     if (lane == 0 && (kind == 4 || kind == 5)) tma_store_wait<0>();
-    if (lane == 0) {
+    if (lane == 0 && (mix < 8 || kind == 6)) {
       const long long per_op = (kind == 1 || kind == 2) ? 4096 : kind == 3 ? 4096 : kind == 7 ? 4096 : 4096;
       atomicAdd((unsigned long long *)&bytes_out[blockIdx.x], (unsigned long long)(ops * per_op * 1000 / (clock64() - t0 + 1)));
     }
@@ -149,7 +155,7 @@ int main(int argc, char **argv) {
   CK(cudaMemcpy(hb.data(), byt, sms * 8, cudaMemcpyDeviceToHost));
   double sum = 0, bsum = 0;
   for (int i = 0; i < sms; ++i) { sum += hc[i]; bsum += hb[i] / 1000.0; }
-  static const char *names[] = {"none", "STS.128", "LDS.128", "LDS.128 broadcast", "bulk store", "bulk reduce f32", "bulk load", "tcgen05.ld"};
+  static const char *names[] = {"none", "STS.128", "LDS.128", "LDS.128 broadcast", "bulk store", "bulk reduce f32", "bulk load", "tcgen05.ld", "reduce + load: load rate", "load only (2 warps)"};
   printf("contention %s kind %d (%-17s) gap %5d grid %3d region %5d KB: %7.2f clk/MMA; bystander traffic %6.1f B/clk/SM\n",
          mma_on ? (ts ? "TS" : "SS") : "--", kind, names[kind], gap, sms, region_kb, sum / sms / n_mma, bsum / sms);
   return 0;
