@@ -15,7 +15,8 @@ FA_B200_F16, FA_B200_BF16, FA_B200_F32 = 0, 1, 2
 _DTYPES = {torch.float16: FA_B200_F16, torch.bfloat16: FA_B200_BF16, torch.float32: FA_B200_F32}
 
 EXPORTED_SYMBOLS = (
-    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_merge", "fa_b200_merge_acc",
+    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_sm_clock", "fa_b200_merge",
+    "fa_b200_merge_acc",
     "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
     "fa_b200_version",
 )
@@ -41,6 +42,8 @@ _lib.fa_b200_bwd.argtypes = [_PP, _PT, _PT, _PT, _PT, _PT, c_void_p, _PT, _PT, _
 _lib.fa_b200_bwd.restype = c_int
 _lib.fa_b200_bwd_workspace_bytes.argtypes = [_PP]
 _lib.fa_b200_bwd_workspace_bytes.restype = c_size_t
+_lib.fa_b200_bwd_sm_clock.argtypes = [_PP, c_void_p, POINTER(ctypes.c_uint64), POINTER(ctypes.c_uint64)]
+_lib.fa_b200_bwd_sm_clock.restype = c_int
 _lib.fa_b200_merge.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]
 _lib.fa_b200_merge.restype = c_int
 _lib.fa_b200_merge_acc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
@@ -137,6 +140,14 @@ def bwd(prob: Problem, q, k, v, o, dout, lse, dq, dk, dv, workspace) -> None:
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q))
     _check(rc, "fa_b200_bwd")
+
+
+def bwd_sm_clock(prob: Problem, workspace) -> tuple:
+    """(SM cycles, nanoseconds) CTA 0 of the last tensor-family backward run with `workspace` spent
+    on its SM; cycles / ns * 1e3 = effective SM clock in MHz under load.  Synchronise first."""
+    cyc, ns = ctypes.c_uint64(0), ctypes.c_uint64(0)
+    _check(_lib.fa_b200_bwd_sm_clock(byref(prob), workspace.data_ptr(), byref(cyc), byref(ns)), "fa_b200_bwd_sm_clock")
+    return int(cyc.value), int(ns.value)
 
 
 def merge(o_a, lse_a, o_b, lse_b) -> None:

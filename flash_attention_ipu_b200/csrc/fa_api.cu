@@ -395,6 +395,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
   bp.lse2 = lse2; bp.delta = delta; bp.sched_counter = counter;
+  bp.clock_out = reinterpret_cast<unsigned long long *>(counter + 2);  // 8-byte aligned, inside the counter's 256-byte slot
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
   bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;
   bp.causal = p->causal; bp.shift = p->q_pos0 - p->kv_pos0;
@@ -525,6 +526,18 @@ int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
     }
   }
   return fail(FA_B200_ERR_UNSUPPORTED, "no kernel for dtype %d, D=%d", p->dtype, p->D);
+}
+
+int fa_b200_bwd_sm_clock(const fa_b200_problem *p, const void *workspace, uint64_t *cycles, uint64_t *ns) {
+  if (int rc = check_problem(p)) return rc;
+  if (!workspace || !cycles || !ns) return fail(FA_B200_ERR_INVALID, "null argument");
+  if (family(p) != 1) return fail(FA_B200_ERR_UNSUPPORTED, "only the tensor-family backward records its SM clock");
+  const uint8_t *ws = reinterpret_cast<const uint8_t *>(workspace);
+  unsigned long long h[2] = {0, 0};
+  FA_CUDA_OK(cudaMemcpy(h, ws + 2 * ws_stat_bytes(p) + ws_acc_bytes(p) + 2 * sizeof(int), sizeof(h), cudaMemcpyDeviceToHost));
+  *cycles = h[0];
+  *ns = h[1];
+  return 0;
 }
 
 int fa_b200_merge(void *o_a, float *lse_a, const void *o_b, const float *lse_b, int64_t rows,

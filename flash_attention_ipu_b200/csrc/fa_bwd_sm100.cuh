@@ -54,6 +54,7 @@ struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
   const float *delta;  // [G][Lq_pad]  -rowsum(O o dO); 0 for padding
   int *sched_counter;  // zeroed by fa_bwd_prep_kernel; next unclaimed item = gridDim.x + counter
+  unsigned long long *clock_out;  // [2]: SM cycles and nanoseconds CTA 0 spent in the kernel (effective SM clock under load)
   int Lq, Lk, H, Lq_pad;
   int Hkv, kv_ratio;   // K/V heads and query heads per K/V head (H = Hkv * kv_ratio; 1 = multi-head)
   int causal, shift;
@@ -157,6 +158,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
   const int num_q_tiles = (p.Lq + 127) / 128;
+  long long clk0 = 0;
+  unsigned long long ns0 = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { clk0 = clock64(); ns0 = global_timer_ns(); }
 
   if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) {
     printf("fa_b200: dynamic shared memory is not 1024-byte aligned\n");
@@ -595,6 +599,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 14) tmem_dealloc<512>(tmem_base);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // a persistent CTA stays on one SM: both counters are that SM's
+    p.clock_out[0] = static_cast<unsigned long long>(clock64() - clk0);
+    p.clock_out[1] = global_timer_ns() - ns0;
+  }
 }
 
 // Pre-kernel: delta = -rowsum(O o dO) (cpp/flash_attention_qkv_packed.cpp:374-377) and

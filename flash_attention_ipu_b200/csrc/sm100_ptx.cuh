@@ -445,6 +445,11 @@ __device__ __forceinline__ float fast_exp2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 // ------------------------------------------------------------------ packed fp32 pairs (FFMA2/FADD2/FMUL2)
 __device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
   uint64_t r;

@@ -23,8 +23,11 @@ class HostStreamedAttention:
     """Reusable pipeline object (device staging buffers and streams are allocated once).
 
     ``run(h_qkv, h_dout, h_out, h_dqkv)``: all four are pinned host tensors, ``h_qkv``/``h_dqkv``
-    of shape (3, G, L, D) and ``h_dout``/``h_out`` of shape (G, L, D); on return (after the
-    internal synchronisation) ``h_out`` holds the attention output and ``h_dqkv`` the gradients.
+    of shape (3, G, L, D) and ``h_dout``/``h_out`` of shape (G, L, D).  With ``sync=True`` (default)
+    the call returns once the last download has landed: ``h_out`` holds the attention output and
+    ``h_dqkv`` the gradients.  With ``sync=False`` the work is only ordered on the current CUDA stream
+    (so that the next step's uploads overlap this step's tail) and the caller must synchronise that
+    stream before reading the host buffers.
     """
 
     def __init__(self, G: int, L: int, D: int, dtype=torch.bfloat16, device: Optional[torch.device] = None,
@@ -45,7 +48,7 @@ class HostStreamedAttention:
         self.ev_done = [torch.cuda.Event() for _ in range(2)]      # results of the chunk ready
         self.res = [None, None]
 
-    def run(self, h_qkv, h_dout, h_out, h_dqkv) -> None:
+    def run(self, h_qkv, h_dout, h_out, h_dqkv, sync: bool = True) -> None:
         for t in (h_qkv, h_dout, h_out, h_dqkv):
             if t.is_cuda or not t.is_pinned():
                 raise ValueError("HostStreamedAttention.run wants pinned host tensors")
@@ -84,3 +87,7 @@ class HostStreamedAttention:
                     self.res[p][1].record_stream(self.s_out)
         cur.wait_stream(self.s_out)
         cur.wait_stream(self.s_in)
+        if sync:
+            done = torch.cuda.Event()
+            done.record(cur)
+            done.synchronize()

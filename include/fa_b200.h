@@ -83,6 +83,13 @@ int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 
 size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p);
 
+/* Measurement hook (no reference counterpart; the reference's C++ benchmark reads
+ * poplar::cycleCount the same way, tests/cpp/test_flash_attention.cpp:236-239): SM cycles and
+ * nanoseconds that CTA 0 of the last tensor-family backward kernel launched with `workspace`
+ * spent on its SM -- cycles / ns = the effective SM clock under load.  Synchronises on the copy;
+ * call after the stream the backward ran on has been synchronised. */
+int fa_b200_bwd_sm_clock(const fa_b200_problem *p, const void *workspace, uint64_t *cycles, uint64_t *ns);
+
 /* LSE merge of two partial results over disjoint key sets (ring-attention hop):
  *   lse = logaddexp(lse_a, lse_b);  o = o_a*exp(lse_a-lse) + o_b*exp(lse_b-lse)
  * written in place into (o_a, lse_a).  rows = B*H*Lq, o_* contiguous [rows][D].

@@ -14,11 +14,17 @@ ROOT = pathlib.Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 
 
-def shard_groups(G: int, world: int, rank: int):
-    """Contiguous, balanced split of G independent groups (what bench.py / a DP launcher does)."""
-    base, rem = divmod(G, world)
-    start = rank * base + min(rank, rem)
-    return start, start + base + (1 if rank < rem else 0)
+def _load_sharding():
+    """The product's sharding module, loaded by path: importing the package itself needs the native
+    library, which is not what this CPU test is about."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("fa_sharding", ROOT / "flash_attention_ipu_b200" / "sharding.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+shard_groups = _load_sharding().shard_groups
 
 
 def _worker(rank, world, port, G, L, D, tmp):
@@ -28,7 +34,8 @@ def _worker(rank, world, port, G, L, D, tmp):
     torch.manual_seed(0)
     qkv = torch.randn(3, G, L, D)
     lo, hi = shard_groups(G, world, rank)
-    out_local = ao.packed_attention_reference(qkv[:, lo:hi])
+    assert _load_sharding().local_groups(qkv, world, rank).shape[1] == hi - lo
+    out_local = ao.packed_attention_reference(_load_sharding().local_groups(qkv, world, rank))
     # no collective on the data path: each rank writes its own shard; only timing is reduced
     torch.save((lo, hi, out_local), f"{tmp}/shard{rank}.pt")
     t = torch.tensor([float(rank + 1)])
