@@ -31,10 +31,18 @@ $(OUT)/liboracle.so: oracle/vanilla_attention.c
 	@mkdir -p $(OUT)
 	$(CC) -O2 -fPIC -shared -Wall -Wextra -o $@ $< -lm
 
-$(OUT)/tests: tests/cuda/test_flash_attention.cu oracle/vanilla_attention.c $(OUT)/libflash_attention.so
+# The C++ test binary (reference: Makefile:25-33 builds build/tests from Catch2's amalgamated
+# sources).  CATCH2_DIR=<a Catch2 v3 checkout> builds against the real thing; without it the
+# TEST_CASE / REQUIRE / "[tag]" surface comes from tests/cuda/catch_shim.hpp.
+CATCH2_DIR ?=
+ifneq ($(CATCH2_DIR),)
+CATCH_FLAGS := -DFA_USE_CATCH2 -I$(CATCH2_DIR)/extras
+CATCH_SRC   := $(CATCH2_DIR)/extras/catch_amalgamated.cpp
+endif
+$(OUT)/tests: tests/cuda/test_flash_attention.cu tests/cuda/catch_shim.hpp oracle/vanilla_attention.c $(OUT)/libflash_attention.so
 	$(CC) -O2 -c -o $(OUT)/vanilla_attention.o oracle/vanilla_attention.c
-	$(NVCC) -std=c++17 -O2 $(ARCH) -Iinclude -o $@ tests/cuda/test_flash_attention.cu $(OUT)/vanilla_attention.o \
-	    -L$(OUT) -lflash_attention -Xlinker -rpath -Xlinker '$$ORIGIN'
+	$(NVCC) -std=c++17 -O2 $(ARCH) -Iinclude $(CATCH_FLAGS) -o $@ tests/cuda/test_flash_attention.cu $(CATCH_SRC) \
+	    $(OUT)/vanilla_attention.o -L$(OUT) -lflash_attention -Xlinker -rpath -Xlinker '$$ORIGIN'
 
 $(OUT)/umma_probe: tests/cuda/umma_probe.cu $(CSRC)/sm100_ptx.cuh
 	@mkdir -p $(OUT)

@@ -15,7 +15,8 @@ FA_B200_F16, FA_B200_BF16, FA_B200_F32 = 0, 1, 2
 _DTYPES = {torch.float16: FA_B200_F16, torch.bfloat16: FA_B200_BF16, torch.float32: FA_B200_F32}
 
 EXPORTED_SYMBOLS = (
-    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_sm_clock", "fa_b200_merge",
+    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_dq_accum", "fa_b200_bwd_sm_clock",
+    "fa_b200_merge",
     "fa_b200_merge_acc",
     "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
     "fa_b200_version",
@@ -42,6 +43,8 @@ _lib.fa_b200_bwd.argtypes = [_PP, _PT, _PT, _PT, _PT, _PT, c_void_p, _PT, _PT, _
 _lib.fa_b200_bwd.restype = c_int
 _lib.fa_b200_bwd_workspace_bytes.argtypes = [_PP]
 _lib.fa_b200_bwd_workspace_bytes.restype = c_size_t
+_lib.fa_b200_bwd_dq_accum.argtypes = _lib.fa_b200_bwd.argtypes
+_lib.fa_b200_bwd_dq_accum.restype = c_int
 _lib.fa_b200_bwd_sm_clock.argtypes = [_PP, c_void_p, POINTER(ctypes.c_uint64), POINTER(ctypes.c_uint64)]
 _lib.fa_b200_bwd_sm_clock.restype = c_int
 _lib.fa_b200_merge.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]
@@ -140,6 +143,21 @@ def bwd(prob: Problem, q, k, v, o, dout, lse, dq, dk, dv, workspace) -> None:
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q))
     _check(rc, "fa_b200_bwd")
+
+
+def bwd_dq_accum(prob: Problem, q, k, v, o, dout, lse, dq_acc, dk, dv, workspace) -> None:
+    """fa_b200_bwd_dq_accum: ``dq_acc`` is an fp32 (B, H, Lq, D) accumulator that receives
+    ``dS K`` (no softmax scale) by in-kernel reduce-add; dk, dv as in :func:`bwd`."""
+    _require_cuda(q, k, v, o, dout, lse, dq_acc, dk, dv, workspace)
+    if dq_acc.dtype != torch.float32:
+        raise RuntimeError("dq_acc must be fp32")
+    with torch.cuda.device(q.device):
+        rc = _lib.fa_b200_bwd_dq_accum(byref(prob), byref(_tensor(q)), byref(_tensor(k)), byref(_tensor(v)),
+                                       byref(_tensor(o)), byref(_tensor(dout)), lse.data_ptr(),
+                                       byref(_tensor(dq_acc)), byref(_tensor(dk)), byref(_tensor(dv)),
+                                       workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                                       _stream(q))
+    _check(rc, "fa_b200_bwd_dq_accum")
 
 
 def bwd_sm_clock(prob: Problem, workspace) -> tuple:

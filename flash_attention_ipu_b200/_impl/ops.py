@@ -47,14 +47,28 @@ qkv_packed_fwd = torch.ops.flash_attention_ipu.qkv_packed_fwd
 qkv_packed_bwd = torch.ops.flash_attention_ipu.qkv_packed_bwd
 
 
+def _like_kernel_view(t):
+    """Shape/stride twin of what csrc/torch_ops.cpp allocates next to an operand: the operand is
+    used in place when D has unit stride and every other dim of size > 1 has a positive, 16-byte
+    aligned stride (``as_bhld``), and the result is ``empty_like`` of that view; otherwise the operand
+    is made contiguous first and the result is contiguous."""
+    es = t.element_size()
+    ok = t.ndim == 4 and t.stride(-1) == 1 and all(
+        t.size(i) == 1 or (t.stride(i) > 0 and (t.stride(i) * es) % 16 == 0) for i in range(t.ndim - 1))
+    if not ok:
+        return t.new_empty(t.shape)
+    like = torch.empty_like(t)
+    return like if like.stride(-1) == 1 else t.new_empty(t.shape)
+
+
 @torch.library.register_fake("flash_attention_ipu::attention_fwd")
 def _(q, k, v, softmax_scale, causal, block_q, block_kv):
-    return torch.empty_like(q), q.new_empty(q.shape[:3], dtype=torch.float32)
+    return _like_kernel_view(q), q.new_empty(q.shape[:3], dtype=torch.float32)
 
 
 @torch.library.register_fake("flash_attention_ipu::attention_bwd")
 def _(dout, q, k, v, out, lse, softmax_scale, causal, block_q, block_kv):
-    return torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    return _like_kernel_view(q), _like_kernel_view(k), _like_kernel_view(v)
 
 
 @torch.library.register_fake("flash_attention_ipu::qkv_packed_fwd")

@@ -57,7 +57,8 @@ def _sdpa_impl(
 
     on_device = (query.is_cuda and query.dtype in _SUPPORTED and query.ndim >= 2
                  and key.dtype == query.dtype and value.dtype == query.dtype
-                 and (query.shape[-1] <= 256) and (query.shape == key.shape or gqa))
+                 and (query.shape[-1] <= 256) and (query.shape == key.shape or gqa)
+                 and (scale is None or scale > 0))  # the kernels want a positive scale; torch accepts any
     if not on_device:
         kwargs = {} if scale is None else {"scale": scale}
         if enable_gqa:

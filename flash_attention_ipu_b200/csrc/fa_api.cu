@@ -59,6 +59,10 @@ int check_problem(const fa_b200_problem *p) {
     return fail(FA_B200_ERR_UNSUPPORTED, "grouped-query attention needs the tensor path (16-bit, D in {64,128})");
   if (p->D > fa::kGenMaxD && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
     return fail(FA_B200_ERR_UNSUPPORTED, "head dim %d > %d", p->D, fa::kGenMaxD);
+  // every kernel folds (tiles x groups) into a 1-D grid
+  const int64_t lmax = p->Lq > p->Lk ? p->Lq : p->Lk;
+  if ((int64_t)p->B * p->H * ((lmax + 63) / 64) > INT32_MAX)
+    return fail(FA_B200_ERR_UNSUPPORTED, "problem too large for a 1-D grid (B*H*ceil(L/64) > 2^31-1)");
   return 0;
 }
 
@@ -212,7 +216,7 @@ int tiled_fwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa
   auto kern = fa::fa_tiled_fwd_kernel<T, DP, kAsync>;
   static std::atomic<uint64_t> smem_ok{0};
   if (int rc = allow_smem(kern, fa::t_fwd_smem<DP>(), smem_ok)) return rc;
-  kern<<<dim3(tiles(p->Lq), (unsigned)(p->B * p->H)), fa::kTThreads, fa::t_fwd_smem<DP>(), st>>>(
+  kern<<<tiles(p->Lq) * (unsigned)(p->B * p->H), fa::kTThreads, fa::t_fwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<T>(o), lse, gparams(p));
   return launched();
 }
@@ -258,11 +262,11 @@ int tiled_bwd_launch(const fa_b200_problem *p, const fa_b200_tensor *q, const fa
   if (int rc = allow_smem(kq, fa::t_bwd_smem<DP>(), smem_ok_q)) return rc;
   if (int rc = allow_smem(kkv, fa::t_bwd_smem<DP>(), smem_ok_kv)) return rc;
   const unsigned groups = (unsigned)(p->B * p->H);
-  kq<<<dim3(tiles(p->Lq), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
+  kq<<<tiles(p->Lq) * groups, fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(o), view<const T>(dout), lse,
       delta, view<T>(dq), gparams(p));  // also writes delta for the next kernel
   if (int rc = launched()) return rc;
-  kkv<<<dim3(tiles(p->Lk), groups), fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
+  kkv<<<tiles(p->Lk) * groups, fa::kTThreads, fa::t_bwd_smem<DP>(), st>>>(
       view<const T>(q), view<const T>(k), view<const T>(v), view<const T>(dout), lse, delta,
       view<T>(dk), view<T>(dv), gparams(p));
   return launched();
@@ -301,58 +305,6 @@ int generic_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 }
 
 // ---------------------------------------------------------------- tensor family: forward
-template <int D, bool kBf16>
-int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
-               const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
-  CUtensorMap tq, tk, tv, to;
-  if (int rc = make_tmap(&tq, q, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
-  if (int rc = make_tmap(&tk, k, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
-  if (int rc = make_tmap(&tv, v, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
-  if (int rc = make_tmap(&to, o, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
-  fa::FwdParams fp;
-  fp.lse = lse;
-  fp.Lq = p->Lq; fp.Lk = p->Lk; fp.H = p->H;
-  fp.kv_ratio = p->H / kv_heads(p);
-  fp.causal = p->causal;
-  fp.shift = p->q_pos0 - p->kv_pos0;
-  fp.scale_log2 = p->softmax_scale * fa::kLog2e;
-  fp.num_pairs = (p->Lq + 2 * fa::kBlockM - 1) / (2 * fa::kBlockM);
-  auto kern = fa::fa_fwd_sm100_kernel<D, kBf16>;
-  static std::atomic<uint64_t> smem_ok{0};  // per instantiation
-  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok)) return rc;
-  const unsigned grid = (unsigned)((int64_t)p->B * p->H * fp.num_pairs);
-#ifdef FA_FWD_TRACE
-  static unsigned long long *d_trace = nullptr;
-  if (!d_trace) { cudaMalloc(&d_trace, 128 * 8); }
-  cudaMemset(d_trace, 0, 128 * 8);
-  fp.trace = d_trace;
-#endif
-  kern<<<grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st>>>(tq, tk, tv, to, fp);
-#ifdef FA_FWD_TRACE
-  if (D == 128 && p->Lq >= 8192) {
-    unsigned long long h[128];
-    cudaStreamSynchronize(st);
-    cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);
-    const unsigned long long t0 = h[0];
-    for (int j = 0; j < 4; ++j) {
-      fprintf(stderr, "trace j=%d:", 10 + j);
-      for (int sl : {16, 0, 17, 18, 19, 20, 21, 1, 2, 22, 9, 12}) fprintf(stderr, " [%d]%lld", sl, (long long)(h[j * 32 + sl] - t0));
-      fprintf(stderr, "\n");
-    }
-  }
-#endif
-  return launched();
-}
-
-// ---------------------------------------------------------------- tensor family: backward
-size_t align256(size_t x) { return (x + 255) / 256 * 256; }
-int lq_pad(const fa_b200_problem *p) { return (p->Lq + 127) / 128 * 128; }
-// workspace: delta[G][Lq_pad] | lse2[G][Lq_pad] | dq_acc[G][Lq][D] (fp32) | work counter, each 256-byte aligned
-size_t ws_stat_bytes(const fa_b200_problem *p) {
-  return align256((size_t)p->B * p->H * lq_pad(p) * sizeof(float));
-}
-size_t ws_acc_bytes(const fa_b200_problem *p) { return align256((size_t)p->B * p->H * p->Lq * p->D * sizeof(float)); }
-
 int sm_count() {  // per device: a process may drive several GPUs
   static std::atomic<int> cached[64];
   int dev = 0;
@@ -365,11 +317,90 @@ int sm_count() {  // per device: a process may drive several GPUs
   return n;
 }
 
+// Work counters of the persistent forward (the backward keeps its counter in its workspace; the
+// forward has none).  A ring of kFwdCounters 4-byte slots per device, allocated once; every launch
+// takes the next slot and zeroes it ON ITS STREAM right before the kernel, so launches on different
+// streams never share a counter unless kFwdCounters of them are in flight at once.
+constexpr int kFwdCounters = 1024;
+int *fwd_counter_slot(cudaStream_t st, int *rc) {
+  static std::atomic<int *> base[64];
+  static std::atomic<unsigned> next{0};
+  static std::mutex mu;
+  int dev = 0;
+  *rc = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { *rc = fail(FA_B200_ERR_CUDA, "cudaGetDevice failed"); return nullptr; }
+  int *b = base[dev & 63].load(std::memory_order_acquire);
+  if (!b) {
+    std::lock_guard<std::mutex> lock(mu);
+    b = base[dev & 63].load(std::memory_order_acquire);
+    if (!b) {
+      if (cudaMalloc(&b, kFwdCounters * sizeof(int)) != cudaSuccess) {
+        *rc = fail(FA_B200_ERR_CUDA, "cudaMalloc of the forward work counters failed");
+        return nullptr;
+      }
+      base[dev & 63].store(b, std::memory_order_release);
+    }
+  }
+  int *slot = b + next.fetch_add(1, std::memory_order_relaxed) % kFwdCounters;
+  if (cudaMemsetAsync(slot, 0, sizeof(int), st) != cudaSuccess) {
+    *rc = fail(FA_B200_ERR_CUDA, "cudaMemsetAsync of the forward work counter failed");
+    return nullptr;
+  }
+  return slot;
+}
+
+template <int D, bool kBf16>
+int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+               const fa_b200_tensor *v, const fa_b200_tensor *o, float *lse, cudaStream_t st) {
+  CUtensorMap tq, tk, tv, to;
+  if (int rc = make_tmap(&to, o, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
+  if (int rc = make_tmap(&tq, q, p->dtype, p->B, p->H, p->Lq, D, fa::kBlockM)) return rc;
+  if (int rc = make_tmap(&tk, k, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
+  if (int rc = make_tmap(&tv, v, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
+  fa::FwdParams fp;
+  fp.lse = lse;
+  fp.Lq = p->Lq; fp.Lk = p->Lk; fp.H = p->H;
+  fp.kv_ratio = p->H / kv_heads(p);
+  fp.causal = p->causal;
+  fp.shift = p->q_pos0 - p->kv_pos0;
+  fp.scale_log2 = p->softmax_scale * fa::kLog2e;
+  fp.num_pairs = (p->Lq + 2 * fa::kBlockM - 1) / (2 * fa::kBlockM);
+  const int64_t items = (int64_t)p->B * p->H * fp.num_pairs;
+  if (items > INT32_MAX) return fail(FA_B200_ERR_UNSUPPORTED, "too many Q tile pairs (%lld)", (long long)items);
+  fp.num_items = (int)items;
+  auto kern = fa::fa_fwd_sm100_kernel<D, kBf16>;
+  static std::atomic<uint64_t> smem_ok{0};  // per instantiation
+  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok)) return rc;
+  // persistent: one CTA per SM (the kernel takes all of an SM's shared memory); with no more items
+  // than SMs every CTA runs exactly one and no counter is needed
+  const int sms = sm_count();
+  fp.sched_counter = nullptr;
+  if (items > sms) {
+    int rc = 0;
+    fp.sched_counter = fwd_counter_slot(st, &rc);
+    if (rc) return rc;
+  }
+  const unsigned grid = (unsigned)(items < sms ? items : sms);
+  kern<<<grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st>>>(tq, tk, tv, to, fp);
+  return launched();
+}
+
+// ---------------------------------------------------------------- tensor family: backward
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+int lq_pad(const fa_b200_problem *p) { return (p->Lq + 127) / 128 * 128; }
+// workspace: delta[G][Lq_pad] | lse2[G][Lq_pad] | dq_acc[G][Lq][D] (fp32) | work counter, each 256-byte aligned
+size_t ws_stat_bytes(const fa_b200_problem *p) {
+  return align256((size_t)p->B * p->H * lq_pad(p) * sizeof(float));
+}
+size_t ws_acc_bytes(const fa_b200_problem *p) { return align256((size_t)p->B * p->H * p->Lq * p->D * sizeof(float)); }
+
 template <int D, bool kBf16>
 int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
                const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
                const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
-               const fa_b200_tensor *dv, void *workspace, cudaStream_t st) {
+               const fa_b200_tensor *dv, void *workspace, cudaStream_t st, bool dq_accum = false) {
+  // dq_accum: `dq` is the CALLER's fp32 (B,H,Lq,D) accumulator; partial dQ tiles are reduce-added
+  // into it as they are (dS K, without softmax_scale): no zero-fill, no convert pass
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   uint8_t *ws = reinterpret_cast<uint8_t *>(workspace);
   float *delta = reinterpret_cast<float *>(ws);
@@ -380,7 +411,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   fa::fa_bwd_prep_kernel<T, D><<<blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st>>>(
       reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
       reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
-      delta, lse2, dq_acc, p->B, p->H, p->Lq, Lp, counter);
+      delta, lse2, dq_accum ? nullptr : dq_acc, p->B, p->H, p->Lq, Lp, counter);
   if (int rc = launched()) return rc;
 
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
@@ -390,7 +421,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tk, k, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tv, v, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdo, dout, p->dtype, p->B, p->H, p->Lq, D, 128)) return rc;
-  if (int rc = make_tmap(&tdq, &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32)) return rc;
+  if (int rc = make_tmap(&tdq, dq_accum ? dq : &acc, FA_B200_F32, p->B, p->H, p->Lq, D, 32)) return rc;
   if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
@@ -428,6 +459,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
             h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6], h[7], (double)h[8] / (h[7] ? h[7] : 1));
   }
 #endif
+  if (dq_accum) return 0;
   // dQ = softmax_scale * dq_acc, cast to the output dtype
   fa::fa_convert_kernel<T><<<148 * 8, 256, 0, st>>>(dq_acc, view<T>(dq), p->B, p->H, p->Lq, D,
                                                      p->softmax_scale);
@@ -526,6 +558,32 @@ int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
     }
   }
   return fail(FA_B200_ERR_UNSUPPORTED, "no kernel for dtype %d, D=%d", p->dtype, p->D);
+}
+
+int fa_b200_bwd_dq_accum(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                         const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                         const float *lse, const fa_b200_tensor *dq_acc, const fa_b200_tensor *dk,
+                         const fa_b200_tensor *dv, void *workspace, size_t workspace_bytes, void *stream) {
+  if (int rc = check_problem(p)) return rc;
+  if (check_tensor(q, "q") || check_tensor(k, "k") || check_tensor(v, "v") || check_tensor(o, "o") ||
+      check_tensor(dout, "dout") || check_tensor(dq_acc, "dq_acc") || check_tensor(dk, "dk") || check_tensor(dv, "dv"))
+    return FA_B200_ERR_INVALID;
+  if (!lse) return fail(FA_B200_ERR_INVALID, "null lse");
+  if (family(p) != 1)
+    return fail(FA_B200_ERR_UNSUPPORTED, "in-place fp32 dQ accumulation needs the tensor path (16-bit, D in {64,128})");
+  if (!workspace || workspace_bytes < fa_b200_bwd_workspace_bytes(p))
+    return fail(FA_B200_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, fa_b200_bwd_workspace_bytes(p));
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return fail(FA_B200_ERR_INVALID, "workspace must be 256-byte aligned");
+  const size_t es = elem_size(p->dtype);
+  if (!(tma_ok(q, es) && tma_ok(k, es) && tma_ok(v, es) && tma_ok(o, es) && tma_ok(dout, es) && tma_ok(dq_acc, 4) &&
+        tma_ok(dk, es) && tma_ok(dv, es)))
+    return fail(FA_B200_ERR_INVALID, "tensor path needs 16-byte aligned pointers and strides (TMA requirement)");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (p->dtype == FA_B200_BF16)
+    return p->D == 128 ? tensor_bwd<128, true>(p, q, k, v, o, dout, lse, dq_acc, dk, dv, workspace, st, true)
+                       : tensor_bwd<64, true>(p, q, k, v, o, dout, lse, dq_acc, dk, dv, workspace, st, true);
+  return p->D == 128 ? tensor_bwd<128, false>(p, q, k, v, o, dout, lse, dq_acc, dk, dv, workspace, st, true)
+                     : tensor_bwd<64, false>(p, q, k, v, o, dout, lse, dq_acc, dk, dv, workspace, st, true);
 }
 
 int fa_b200_bwd_sm_clock(const fa_b200_problem *p, const void *workspace, uint64_t *cycles, uint64_t *ns) {

@@ -633,9 +633,11 @@ fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T
     const T *de = reinterpret_cast<const T *>(&dv);
     #pragma unroll
     for (int e = 0; e < 8; ++e) s = fmaf(static_cast<float>(oe[e]), static_cast<float>(de[e]), s);
-    float4 *acc = reinterpret_cast<float4 *>(dq_acc + (static_cast<int64_t>(g) * Lq + r) * D + sub * 8);
-    acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-    acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (dq_acc) {  // nullptr: the caller owns the accumulator and keeps adding to it (ring hops)
+      float4 *acc = reinterpret_cast<float4 *>(dq_acc + (static_cast<int64_t>(g) * Lq + r) * D + sub * 8);
+      acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+      acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     const float l = lse[static_cast<int64_t>(g) * Lq + r];
     l2 = (l == -INFINITY) ? -INFINITY : -l * kLog2e;
   }

@@ -227,8 +227,10 @@ fa_tiled_fwd_kernel(View<const T> q, View<const T> k, View<const T> v, View<T> o
   constexpr int LD = DP + 4, NC = DP / 32;
   float *Qs = tsm, *Ks = Qs + kTB * LD, *Vs = Ks + kTB * LD, *Ps = Vs + kTB * LD;
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  const int g = blockIdx.y, b = g / p.H, h = g % p.H;
-  const int m0 = (gridDim.x - 1 - blockIdx.x) * kTB;  // longest (latest) causal rows first
+  // 1-D grid (tiles x groups folded: gridDim.y stops at 65 535 groups), tile index fastest
+  const int nt = (p.Lq + kTB - 1) / kTB;
+  const int g = blockIdx.x / nt, b = g / p.H, h = g % p.H;
+  const int m0 = (nt - 1 - static_cast<int>(blockIdx.x % nt)) * kTB;  // longest (latest) causal rows first
   // Q goes to shared memory unscaled (same asynchronous copy as the streamed tiles, in flight
   // together with K(0)); softmax_scale * log2(e) is folded into the exponent's FFMA instead.
   t_stream_tile<T, DP, kAsync>(Qs, q.row(b, h, 0), q.sl, m0, p.Lq, p.D);
@@ -318,8 +320,9 @@ fa_tiled_bwd_dq_kernel(View<const T> q, View<const T> k, View<const T> v, View<c
   constexpr int LD = DP + 4, NC = DP / 32;
   float *Qs = tsm, *Ds = Qs + kTB * LD, *Ks = Ds + kTB * LD, *Vs = Ks + kTB * LD, *Ps = Vs + kTB * LD;
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  const int g = blockIdx.y, b = g / p.H, h = g % p.H;
-  const int m0 = (gridDim.x - 1 - blockIdx.x) * kTB;
+  const int nt = (p.Lq + kTB - 1) / kTB;
+  const int g = blockIdx.x / nt, b = g / p.H, h = g % p.H;
+  const int m0 = (nt - 1 - static_cast<int>(blockIdx.x % nt)) * kTB;
   int hi = p.Lk;
   if (p.causal) hi = min(hi, m0 + kTB + p.shift);
   const T *kslab = k.row(b, h, 0), *vslab = v.row(b, h, 0);
@@ -412,8 +415,9 @@ fa_tiled_bwd_dkv_kernel(View<const T> q, View<const T> k, View<const T> v, View<
   float *Ks = tsm, *Vs = Ks + kTB * LD, *Qs = Vs + kTB * LD, *Ds = Qs + kTB * LD, *Ps = Ds + kTB * LD;
   float *lse2s = Ps + kTB * kTLdp, *dls = lse2s + kTB;
   const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-  const int g = blockIdx.y, b = g / p.H, h = g % p.H;
-  const int n0 = blockIdx.x * kTB;  // earliest keys have the most causal work
+  const int nt = (p.Lk + kTB - 1) / kTB;
+  const int g = blockIdx.x / nt, b = g / p.H, h = g % p.H;
+  const int n0 = static_cast<int>(blockIdx.x % nt) * kTB;  // earliest keys have the most causal work
   // stationary K, V: unscaled, copied asynchronously together with the first dO tile
   t_stream_tile<T, DP, kAsync>(Ks, k.row(b, h, 0), k.sl, n0, p.Lk, p.D);
   t_stream_tile<T, DP, kAsync>(Vs, v.row(b, h, 0), v.sl, n0, p.Lk, p.D);

@@ -19,6 +19,7 @@
 #include <torch/library.h>
 
 #include <tuple>
+#include <vector>
 
 #include "../../include/fa_b200.h"
 
@@ -42,16 +43,50 @@ void require_cuda(std::initializer_list<const Tensor *> ts) {
                 "flash_attention_ipu_b200 runs on CUDA (sm_100a) tensors only; there is no CPU path");
 }
 
-// (B,H,L,D) view the kernels can address in place: unit stride on D, 16-byte aligned base and
-// strides (the TMA path); anything else is made contiguous.
+// (B,H,L,D) view the kernels can address in place: unit stride on D, 16-byte aligned base, and for
+// every other dim of size > 1 a positive, 16-byte aligned stride (the TMA path; an expanded dim has
+// stride 0 and is materialised).  Size-1 dims never enter the address arithmetic, whatever
+// stride torch reports for them: they are re-strided to the dense value so that the descriptor
+// encoder sees legal numbers.  Anything else is made contiguous.
 Tensor as_bhld(const Tensor &t) {
   const int64_t es = t.element_size();
-  bool ok = t.stride(-1) == 1 && reinterpret_cast<uintptr_t>(t.data_ptr()) % 16 == 0;
-  for (int64_t i = 0; ok && i + 1 < t.dim(); ++i) ok = (t.stride(i) * es) % 16 == 0;
-  return ok ? t : t.contiguous();
+  bool ok = t.dim() == 4 && t.stride(-1) == 1 && reinterpret_cast<uintptr_t>(t.data_ptr()) % 16 == 0;
+  bool restride = false;
+  for (int64_t i = 0; ok && i + 1 < t.dim(); ++i) {
+    if (t.size(i) > 1) ok = t.stride(i) > 0 && (t.stride(i) * es) % 16 == 0;
+    else if (t.stride(i) <= 0 || (t.stride(i) * es) % 16) restride = true;
+  }
+  if (!ok) return t.contiguous();
+  if (!restride) return t;
+  std::vector<int64_t> st(t.strides().begin(), t.strides().end());
+  for (int64_t i = t.dim() - 2; i >= 0; --i)
+    if (t.size(i) == 1) st[i] = st[i + 1] * t.size(i + 1);  // dense value; never used for addressing
+  return t.as_strided(t.sizes(), st);
 }
 
 fa_b200_tensor desc(const Tensor &t) { return fa_b200_tensor{t.data_ptr(), t.stride(0), t.stride(1), t.stride(2)}; }
+
+// q, k, v (and out / dout / lse when given) must describe ONE problem: same dtype, device, head
+// dim, batch; v shaped like k; out / dout shaped like q; lse fp32 (B, H, Lq)
+void check_operands(const Tensor &q, const Tensor &k, const Tensor &v, const Tensor *out, const Tensor *dout,
+                    const Tensor *lse) {
+  TORCH_CHECK(q.dim() == 4 && k.dim() == 4 && v.dim() == 4, "expected (B, H, L, D) operands");
+  TORCH_CHECK(k.scalar_type() == q.scalar_type() && v.scalar_type() == q.scalar_type(),
+              "q, k, v must share a dtype, got ", q.scalar_type(), " ", k.scalar_type(), " ", v.scalar_type());
+  TORCH_CHECK(k.device() == q.device() && v.device() == q.device(), "q, k, v must be on one device");
+  TORCH_CHECK(k.size(0) == q.size(0) && k.size(3) == q.size(3), "k of shape ", k.sizes(), " does not match q ", q.sizes());
+  TORCH_CHECK(v.sizes() == k.sizes(), "v of shape ", v.sizes(), " does not match k ", k.sizes());
+  for (const Tensor *t : {out, dout}) {
+    if (!t) continue;
+    TORCH_CHECK(t->sizes() == q.sizes(), "out / dout of shape ", t->sizes(), " does not match q ", q.sizes());
+    TORCH_CHECK(t->scalar_type() == q.scalar_type() && t->device() == q.device(), "out / dout must match q's dtype and device");
+  }
+  if (lse) {
+    TORCH_CHECK(lse->scalar_type() == at::kFloat && lse->device() == q.device(), "lse must be an fp32 tensor on q's device");
+    TORCH_CHECK(lse->numel() == q.size(0) * q.size(1) * q.size(2), "lse has ", lse->numel(), " elements, expected B*H*Lq = ",
+                q.size(0) * q.size(1) * q.size(2));
+  }
+}
 
 fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, double scale, int64_t block_q,
                              int64_t block_kv) {
@@ -104,6 +139,7 @@ void run_bwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const T
 std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, const Tensor &v_, double scale,
                                          bool causal, int64_t block_q, int64_t block_kv) {
   require_cuda({&q_, &k_, &v_});
+  check_operands(q_, k_, v_, nullptr, nullptr, nullptr);
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_);
   Tensor out = at::empty_like(q);  // keeps q's (possibly (B,L,H,D)-transposed) dense layout
   if (out.stride(-1) != 1) out = at::empty(q.sizes(), q.options());
@@ -113,9 +149,11 @@ std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, con
 }
 
 std::tuple<Tensor, Tensor, Tensor> attention_bwd(const Tensor &dout_, const Tensor &q_, const Tensor &k_,
-                                                 const Tensor &v_, const Tensor &out_, const Tensor &lse,
+                                                 const Tensor &v_, const Tensor &out_, const Tensor &lse_,
                                                  double scale, bool causal, int64_t block_q, int64_t block_kv) {
-  require_cuda({&dout_, &q_, &k_, &v_, &out_, &lse});
+  require_cuda({&dout_, &q_, &k_, &v_, &out_, &lse_});
+  check_operands(q_, k_, v_, &out_, &dout_, &lse_);
+  const Tensor lse = lse_.contiguous();  // the kernels index it as a dense [B*H][Lq] array
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_), out = as_bhld(out_), dout = as_bhld(dout_);
   const Tensor dq = at::empty_like(q), dk = at::empty_like(k), dv = at::empty_like(v);
   run_bwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out, dout, lse, dq, dk, dv);
@@ -136,9 +174,16 @@ std::tuple<Tensor, Tensor> qkv_packed_fwd(const Tensor &qkv_, double scale, bool
   return {out, lse};
 }
 
-Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out_, const Tensor &lse,
+Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out_, const Tensor &lse_,
                       double scale, bool causal, int64_t block_q, int64_t block_kv) {
-  require_cuda({&dout_, &qkv_, &out_, &lse});
+  require_cuda({&dout_, &qkv_, &out_, &lse_});
+  TORCH_CHECK(qkv_.dim() == 4 && qkv_.size(0) == 3, "expected a packed (3, G, L, D) tensor");
+  TORCH_CHECK(dout_.dim() == 3 && out_.dim() == 3 && dout_.sizes() == out_.sizes() && out_.size(0) == qkv_.size(1) &&
+                  out_.size(1) == qkv_.size(2) && out_.size(2) == qkv_.size(3),
+              "out / dout must be (G, L, D) tensors matching the packed qkv ", qkv_.sizes());
+  TORCH_CHECK(dout_.scalar_type() == qkv_.scalar_type() && out_.scalar_type() == qkv_.scalar_type(), "dtype mismatch");
+  TORCH_CHECK(lse_.scalar_type() == at::kFloat && lse_.numel() == qkv_.size(1) * qkv_.size(2), "lse must be fp32 (G, L)");
+  const Tensor lse = lse_.contiguous();
   const Tensor qkv = qkv_.contiguous(), dout = dout_.contiguous(), out = out_.contiguous();
   const Tensor q = qkv[0].unsqueeze(0), k = qkv[1].unsqueeze(0), v = qkv[2].unsqueeze(0);
   const Tensor dqkv = at::empty_like(qkv);  // gradients land directly in the packed buffer

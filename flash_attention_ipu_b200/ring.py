@@ -82,6 +82,23 @@ class NativeBlocks:
         from ._impl import ops
         return ops.attention_bwd(dout, q, k, v, out, lse, scale, causal, 0, 0)  # (dq, dk, dv)
 
+    def bwd_block_accum(self, dout, q, k, v, out, lse, causal: bool, scale: float, dq_acc):
+        """Backward of one block with dQ reduce-added in place into the fp32 accumulator rows
+        ``dq_acc`` (WITHOUT softmax_scale: the ring applies it once at the end), through the C ABI
+        (``fa_b200_bwd_dq_accum``).  Returns (dk, dv) in the kernel dtype, or None when the
+        problem is off the tensor path (the caller then uses :meth:`bwd_block` and adds)."""
+        from ._impl import native
+        if q.dtype not in (torch.bfloat16, torch.float16) or q.shape[-1] not in (64, 128):
+            return None
+        prob = native.make_problem(q, k, causal, scale)
+        if native.kernel_family(prob) != 1:
+            return None
+        lse = lse.contiguous()
+        dk, dv = torch.empty_like(k, memory_format=torch.contiguous_format), torch.empty_like(v, memory_format=torch.contiguous_format)
+        ws = torch.empty(native.bwd_workspace_bytes(prob), dtype=torch.uint8, device=q.device)
+        native.bwd_dq_accum(prob, q, k, v, out, dout, lse, dq_acc, dk, dv, ws)
+        return dk, dv
+
     def merge_acc(self, o_acc, lse_acc, o_b, lse_b, row0: int) -> None:
         from ._impl import native
         G = o_acc.shape[0] * o_acc.shape[1]
@@ -111,10 +128,20 @@ def _bwd_hop(blocks, rank: int, src: int, q, kv, out, dout, lse, lse_hi, dq_acc,
     accumulator once it has arrived)."""
     qr, kr, causal = hop_plan(rank, src)
     lse_q = lse_hi if qr == "hi" else lse
-    dq, dk, dv = blocks.bwd_block(_rows(dout, qr), _rows(q, qr), _rows(kv[0], kr), _rows(kv[1], kr),
-                                  _rows(out, qr), lse_q, causal, scale)
-    _rows(dq_acc, qr).add_(dq)
+    args = (_rows(dout, qr), _rows(q, qr), _rows(kv[0], kr), _rows(kv[1], kr), _rows(out, qr), lse_q, causal, scale)
+    fused = getattr(blocks, "bwd_block_accum", None)
+    res = fused(*args, _rows(dq_acc, qr)) if fused is not None else None
+    if res is not None:   # dQ went straight into the accumulator (unscaled: see _finish_dq)
+        dk, dv = res
+    else:
+        dq, dk, dv = blocks.bwd_block(*args)
+        _rows(dq_acc, qr).add_(dq, alpha=1.0 / scale)  # keep the accumulator in the unscaled convention
     return kr, dk, dv
+
+
+def _finish_dq(dq_acc, scale: float, dtype):
+    """The fp32 dQ accumulator holds sum(dS K) over all hops; softmax_scale is applied once here."""
+    return dq_acc.mul_(scale).to(dtype)
 
 
 # ------------------------------------------------------------------ ring exchange (real P2P)
@@ -186,7 +213,7 @@ def _ring_backward(blocks, group, q, k, v, out, lse, dout, scale: float):
     if dkv_xch is not None:
         dkv_xch.wait()
     home = dkv[world % 2] if world > 1 else dkv[0]
-    return dq_acc.to(q.dtype), home[0].to(k.dtype), home[1].to(v.dtype)
+    return _finish_dq(dq_acc, scale, q.dtype), home[0].to(k.dtype), home[1].to(v.dtype)
 
 
 class _RingAttention(torch.autograd.Function):
@@ -259,6 +286,6 @@ def ring_attention_emulated(q_shards: Sequence[torch.Tensor], k_shards: Sequence
                                   lse_hi, dq_acc, scale)
             _rows(dkv[src][0], kr).add_(dk)
             _rows(dkv[src][1], kr).add_(dv)
-        dqs.append(dq_acc.to(q.dtype))
+        dqs.append(_finish_dq(dq_acc, scale, q.dtype))
     grads = [(dqs[r], dkv[r][0].to(k_shards[r].dtype), dkv[r][1].to(v_shards[r].dtype)) for r in range(world)]
     return outs, grads

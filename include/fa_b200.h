@@ -83,6 +83,18 @@ int fa_b200_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 
 size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p);
 
+/* Backward of one block of a larger (sequence-sharded) problem, dQ accumulated in place: as
+ * fa_b200_bwd, except that `dq_acc` is the caller's fp32 (B,H,Lq,D) accumulator (element strides,
+ * unit stride on D) and every partial dQ tile is reduce-added into it WITHOUT softmax_scale
+ * (dq_acc += dS K; multiply by softmax_scale once, after the last block).  It is neither zeroed
+ * nor converted, so the ring's hops need no separate add pass and dQ is rounded to 16 bits once.
+ * Cross-device form of the `dQ +=` inside the reference's loop
+ * (cpp/flash_attention_qkv_packed.cpp:470).  Tensor path only (16-bit dtype, D in {64, 128}). */
+int fa_b200_bwd_dq_accum(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                         const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                         const float *lse, const fa_b200_tensor *dq_acc, const fa_b200_tensor *dk,
+                         const fa_b200_tensor *dv, void *workspace, size_t workspace_bytes, void *stream);
+
 /* Measurement hook (no reference counterpart; the reference's C++ benchmark reads
  * poplar::cycleCount the same way, tests/cpp/test_flash_attention.cpp:236-239): SM cycles and
  * nanoseconds that CTA 0 of the last tensor-family backward kernel launched with `workspace`

@@ -2,7 +2,11 @@
 // reference's Catch2 binary (tests/cpp/test_flash_attention.cpp:243-313): same case matrix and
 // the same max-abs thresholds, plus bf16.  Expected values come from the plain-C oracle
 // (oracle/vanilla_attention.c, a restatement of cpp/vanilla_attention.cpp) evaluated on the
-// same (dtype-rounded) inputs.  Usage: build/tests [substring-filter] ; exit code = #failures.
+// same (dtype-rounded) inputs.  TEST_CASEs carry the reference's tags: [attention],
+// [attentionGrad], [attentionperf] (the latter hidden, "[.]", as a benchmark should be: it runs
+// only when asked for).  Usage: build/tests ["[tag]" | name-substring | --list-tests];
+// exit code = number of failed test cases.  Builds against real Catch2 with
+// `make CATCH2_DIR=...`, else against tests/cuda/catch_shim.hpp.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -13,6 +17,12 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include "fa_b200.h"
+#ifdef FA_USE_CATCH2
+#include <catch_amalgamated.hpp>
+#else
+#define FA_CATCH_SHIM_MAIN
+#include "catch_shim.hpp"
+#endif
 
 extern "C" int oracle_vanilla_attention_fwd(const float *, float *, float *, int, int, int, int);
 extern "C" int oracle_vanilla_attention_bwd(const float *, const float *, float *, int, int, int, int);
@@ -62,17 +72,14 @@ static double max_abs_err(const std::vector<float> &a, const float *b, size_t n)
 }
 
 static const char *dname(int dt) { return dt == FA_B200_F32 ? "fp32" : dt == FA_B200_F16 ? "fp16" : "bf16"; }
-static std::string g_filter;
-static int g_failed = 0, g_run = 0;
 
 // One case: forward (and optionally backward) vs the oracle.  num_chunks_* only feed the hints.
-static void run_case(const char *what, int G, int L, int D, int ncq, int nckv, int dtype, int causal,
+// Returns true when every error is within its threshold.
+static bool run_case(const char *what, int G, int L, int D, int ncq, int nckv, int dtype, int causal,
                      bool backward, double tol_fwd, double tol_bwd) {
   char name[160];
   snprintf(name, sizeof name, "%s G=%d L=%d D=%d chunks=%dx%d %s %s", what, G, L, D, ncq, nckv,
            dname(dtype), causal ? "causal" : "full");
-  if (!g_filter.empty() && std::string(name).find(g_filter) == std::string::npos) return;
-  ++g_run;
   const size_t GLD = (size_t)G * L * D, es = dtype == FA_B200_F32 ? 4 : 2;
   Rng rng(1234 + L * 31 + D);
   std::vector<float> qkv(3 * GLD), grad(GLD);
@@ -125,33 +132,110 @@ static void run_case(const char *what, int G, int L, int D, int ncq, int nckv, i
   if (backward) printf("  dQ=%.3g dK=%.3g dV=%.3g (tol %.0e)", eb[0], eb[1], eb[2], tol_bwd);
   printf("\n");
   fflush(stdout);
-  if (!ok) ++g_failed;
   CK(cudaFree(d_qkv)); CK(cudaFree(d_o)); CK(cudaFree(d_do)); CK(cudaFree(d_dqkv)); CK(cudaFree(d_lse));
+  return ok;
 }
 
-int main(int argc, char **argv) {
-  if (argc > 1) g_filter = argv[1];
-  // --- reference matrix, fp32 (test_flash_attention.cpp:245-259 fwd 1e-5; :273-287 bwd 1e-4)
-  const int small[][2] = {{1, 1}, {2, 1}, {1, 2}, {2, 2}, {3, 2}, {2, 3}, {3, 3}};
-  for (auto &c : small) run_case("ref-matrix", 4, 6, 2, c[0], c[1], FA_B200_F32, 1, true, 1e-5, 1e-4);
-  const int mid[][2] = {{2, 2}, {4, 2}, {2, 4}, {4, 4}};
-  for (auto &c : mid) run_case("ref-matrix", 8, 256, 128, c[0], c[1], FA_B200_F32, 1, true, 1e-5, 1e-4);
-  // --- reference matrix, half precision (:261-267 fwd 1e-2; :289-295 bwd 1.0); fp16 and bf16.
-  // G reduced 8 -> 2 to keep the scalar CPU oracle in seconds.
-  for (int dt : {FA_B200_F16, FA_B200_BF16})
-    for (auto &c : mid) run_case("ref-matrix", 2, 2048, 128, c[0], c[1], dt, 1, true, 1e-2, 1.0);
-  // --- tensor-path shapes: single tile, tile pair, ragged tails, D=64, non-causal extension
-  for (int dt : {FA_B200_BF16, FA_B200_F16}) {
-    run_case("tile", 1, 128, 128, 1, 1, dt, 0, true, 1e-2, 1e-1);
-    run_case("tile", 1, 128, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
-    run_case("tile", 2, 256, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
-    run_case("tile", 2, 512, 64, 1, 1, dt, 1, true, 1e-2, 1e-1);
-    run_case("tile", 3, 1024, 64, 4, 4, dt, 1, true, 1e-2, 1e-1);
-    run_case("tile", 2, 512, 64, 4, 2, dt, 0, true, 1e-2, 1e-1);
-    run_case("ragged", 2, 200, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
-    run_case("ragged", 2, 331, 64, 1, 1, dt, 0, true, 1e-2, 1e-1);
-    run_case("ragged", 1, 8, 128, 1, 1, dt, 1, true, 1e-2, 1e-1);
+// Counterpart of benchmark_forward (tests/cpp/test_flash_attention.cpp:170-241, which prints
+// poplar::cycleCount): CUDA-event time of the forward (and forward + backward) on device-resident
+// random inputs, printed with the achieved TFLOP/s.
+static void benchmark_case(int G, int L, int D, int ncq, int nckv, int dtype) {
+  const size_t GLD = (size_t)G * L * D, es = dtype == FA_B200_F32 ? 4 : 2;
+  Rng rng(99 + L);
+  std::vector<float> qkv(3 * GLD), grad(GLD);
+  for (size_t i = 0; i < 3 * GLD; ++i) qkv[i] = rng.normal() * (i < GLD ? 1.0f / std::sqrt((float)D) : 1.f);
+  for (size_t i = 0; i < GLD; ++i) grad[i] = rng.normal();
+  void *d_qkv, *d_o, *d_do, *d_dqkv, *d_ws; float *d_lse;
+  CK(cudaMalloc(&d_qkv, 3 * GLD * es)); CK(cudaMalloc(&d_o, GLD * es)); CK(cudaMalloc(&d_do, GLD * es));
+  CK(cudaMalloc(&d_dqkv, 3 * GLD * es)); CK(cudaMalloc(&d_lse, (size_t)G * L * 4));
+  to_device(qkv, dtype, d_qkv); to_device(grad, dtype, d_do);
+  fa_b200_problem p{};
+  p.B = 1; p.H = G; p.Lq = L; p.Lk = L; p.D = D; p.dtype = dtype; p.causal = 1;
+  p.softmax_scale = 1.f; p.block_q_hint = L / ncq; p.block_kv_hint = L / nckv;
+  auto T = [&](void *base, int which) {
+    return fa_b200_tensor{(char *)base + which * GLD * es, (int64_t)GLD, (int64_t)L * D, (int64_t)D};
+  };
+  fa_b200_tensor q = T(d_qkv, 0), k = T(d_qkv, 1), v = T(d_qkv, 2), o = T(d_o, 0), dout = T(d_do, 0);
+  fa_b200_tensor dq = T(d_dqkv, 0), dk = T(d_dqkv, 1), dv = T(d_dqkv, 2);
+  const size_t wsb = fa_b200_bwd_workspace_bytes(&p);
+  CK(cudaMalloc(&d_ws, wsb));
+  cudaEvent_t e0, e1, e2;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
+  const int reps = 20;
+  float ms_f = 0, ms_fb = 0;
+  for (int pass = 0; pass < 2; ++pass) {  // pass 0 = warm-up
+    CK(cudaEventRecord(e0));
+    for (int r = 0; r < reps; ++r) REQUIRE(fa_b200_fwd(&p, &q, &k, &v, &o, d_lse, nullptr) == 0);
+    CK(cudaEventRecord(e1));
+    for (int r = 0; r < reps; ++r) {
+      REQUIRE(fa_b200_fwd(&p, &q, &k, &v, &o, d_lse, nullptr) == 0);
+      REQUIRE(fa_b200_bwd(&p, &q, &k, &v, &o, &dout, d_lse, &dq, &dk, &dv, d_ws, wsb, nullptr) == 0);
+    }
+    CK(cudaEventRecord(e2));
+    CK(cudaEventSynchronize(e2));
+    CK(cudaEventElapsedTime(&ms_f, e0, e1)); CK(cudaEventElapsedTime(&ms_fb, e1, e2));
   }
-  printf("%d cases run, %d failed\n", g_run, g_failed);
-  return g_failed;
+  const double flop_f = 4.0 * G * (double)L * L * D * 0.5;
+  fprintf(stderr, "Time= %.3f us fwd (%.1f TFLOP/s), %.3f us fwd+bwd (%.1f TFLOP/s) (for: %s QKV[%d, %d, %d], Chunks[%d, %d])\n",
+          1e3 * ms_f / reps, flop_f / (ms_f / reps * 1e-3) / 1e12, 1e3 * ms_fb / reps,
+          3.5 * flop_f / (ms_fb / reps * 1e-3) / 1e12, dname(dtype), G, L, D, ncq, nckv);
+  CK(cudaFree(d_qkv)); CK(cudaFree(d_o)); CK(cudaFree(d_do)); CK(cudaFree(d_dqkv)); CK(cudaFree(d_lse)); CK(cudaFree(d_ws));
+}
+
+static const int kSmall[][2] = {{1, 1}, {1, 2}, {2, 1}, {2, 2}, {2, 3}, {3, 2}, {3, 3}};
+static const int kMid[][2] = {{2, 2}, {2, 4}, {4, 2}, {4, 4}};
+
+// tests/cpp/test_flash_attention.cpp:243-269 (forward thresholds 1e-5 fp32, 1e-2 half)
+TEST_CASE("compare vanillaAttention vs flashAttention output", "[attention]") {
+  SECTION("float32 4x6x6 test cases") {
+    for (auto &c : kSmall) REQUIRE(run_case("fwd", 4, 6, 2, c[0], c[1], FA_B200_F32, 1, false, 1e-5, 0));
+  }
+  SECTION("float32 8x256x256 test cases") {
+    for (auto &c : kMid) REQUIRE(run_case("fwd", 8, 256, 128, c[0], c[1], FA_B200_F32, 1, false, 1e-5, 0));
+  }
+  SECTION("float16 / bfloat16 2x2048x2048 test cases") {  // G 8 -> 2: the scalar CPU oracle stays in seconds
+    for (int dt : {FA_B200_F16, FA_B200_BF16})
+      for (auto &c : kMid) REQUIRE(run_case("fwd", 2, 2048, 128, c[0], c[1], dt, 1, false, 1e-2, 0));
+  }
+}
+
+// tests/cpp/test_flash_attention.cpp:271-297 (gradient thresholds 1e-4 fp32, 1.0 half)
+TEST_CASE("compare vanillaAttentionGrad vs flashAttentionGrad output", "[attentionGrad]") {
+  SECTION("float32 4x6x6 test cases") {
+    for (auto &c : kSmall) REQUIRE(run_case("grad", 4, 6, 2, c[0], c[1], FA_B200_F32, 1, true, 1e-5, 1e-4));
+  }
+  SECTION("float32 8x256x256 test cases") {
+    for (auto &c : kMid) REQUIRE(run_case("grad", 8, 256, 128, c[0], c[1], FA_B200_F32, 1, true, 1e-5, 1e-4));
+  }
+  SECTION("float16 / bfloat16 2x2048x2048 test cases") {
+    for (int dt : {FA_B200_F16, FA_B200_BF16})
+      for (auto &c : kMid) REQUIRE(run_case("grad", 2, 2048, 128, c[0], c[1], dt, 1, true, 1e-2, 1.0));
+  }
+}
+
+// not in the reference: shapes that exercise the tcgen05 kernels' edges (single tile, tile pair,
+// ragged tails, D = 64, the non-causal extension), tighter gradient threshold
+TEST_CASE("tensor-path tile shapes through the C ABI", "[attention][attentionGrad][tiles]") {
+  for (int dt : {FA_B200_BF16, FA_B200_F16}) {
+    CHECK(run_case("tile", 1, 128, 128, 1, 1, dt, 0, true, 1e-2, 1e-1));
+    CHECK(run_case("tile", 1, 128, 128, 1, 1, dt, 1, true, 1e-2, 1e-1));
+    CHECK(run_case("tile", 2, 256, 128, 1, 1, dt, 1, true, 1e-2, 1e-1));
+    CHECK(run_case("tile", 2, 512, 64, 1, 1, dt, 1, true, 1e-2, 1e-1));
+    CHECK(run_case("tile", 3, 1024, 64, 4, 4, dt, 1, true, 1e-2, 1e-1));
+    CHECK(run_case("tile", 2, 512, 64, 4, 2, dt, 0, true, 1e-2, 1e-1));
+    CHECK(run_case("ragged", 2, 200, 128, 1, 1, dt, 1, true, 1e-2, 1e-1));
+    CHECK(run_case("ragged", 2, 331, 64, 1, 1, dt, 0, true, 1e-2, 1e-1));
+    CHECK(run_case("ragged", 1, 8, 128, 1, 1, dt, 1, true, 1e-2, 1e-1));
+  }
+}
+
+// tests/cpp/test_flash_attention.cpp:299-313 (prints a time per case to stderr; hidden: run with "[attentionperf]")
+TEST_CASE("benchmark flashAttention performance", "[.][attentionperf]") {
+  SECTION("float32 8x256x256 cases") {
+    for (auto &c : kMid) benchmark_case(8, 256, 128, c[0], c[1], FA_B200_F32);
+  }
+  SECTION("float16 8x2048x256 cases") {
+    for (auto &c : kMid) benchmark_case(8, 2048, 128, c[0], c[1], FA_B200_F16);
+  }
+  SECTION("bfloat16 128x8192x128 (BASELINE config 3)") { benchmark_case(128, 8192, 128, 8, 8, FA_B200_BF16); }
 }
