@@ -62,7 +62,17 @@ $(OUT)/exp_rate: tests/cuda/exp_rate.cu $(CSRC)/sm100_ptx.cuh
 	@mkdir -p $(OUT)
 	$(NVCC) -std=c++17 -O3 -lineinfo $(ARCH) -o $@ $<
 
+# SASS evidence that the hot kernels are tcgen05 / TMEM / TMA code (mnemonics: B200_PROFILING.md)
+sass-summary: $(OUT)/libflash_attention.so
+	@mkdir -p profiles
+	@{ echo "# cuobjdump -sass $(OUT)/libflash_attention.so | grep -c <mnemonic>   (make sass-summary)"; \
+	   cuobjdump -sass $(OUT)/libflash_attention.so > $(OUT)/lib.sass; \
+	   for m in UTCHMMA UTCBAR LDTM STTM UTMALDG UTMASTG UTMAREDG UTMAPF UBLKCP SYNCS.ARRIVE USETMAXREG FFMA2 FADD2 FMUL2 MUFU.EX2; do \
+	     printf "%-14s %s\n" $$m $$(grep -c "$$m" $(OUT)/lib.sass); done; \
+	   echo "# kernels:"; cuobjdump -sass $(OUT)/libflash_attention.so | grep -oE "Function : [A-Za-z0-9_]+" | sed 's/Function : //' | c++filt | grep -E "sm100|prep|convert" | sort | uniq -c; \
+	 } > profiles/sass_summary.txt; cat profiles/sass_summary.txt
+
 clean:
 	rm -rf $(OUT)
 
-.PHONY: all clean
+.PHONY: all clean sass-summary

@@ -49,7 +49,11 @@ def measured_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe).
+    One long-lived nvidia-smi in loop mode (a fresh process per sample is too slow for regions of a
+    few hundred ms).  The process is created in start() -- not in the thread -- and start() waits
+    for its first sample, so that summary() can always stop it: a sampler left running polls the
+    driver every 20 ms and slows every later CUDA call of the process."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -58,12 +62,21 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.samples, self.proc = index, [], None
 
-    def run(self):
-        # one long-lived nvidia-smi in loop mode (a fresh process per sample is too slow for
-        # timed regions of a few hundred ms)
+    def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-i", str(self.index), "-lms", "20"], stdout=subprocess.PIPE, text=True)
+        except Exception:
+            self.proc = None
+        super().start()
+        t0 = time.time()
+        while self.proc is not None and not self.samples and time.time() - t0 < 5.0:
+            time.sleep(0.05)
+
+    def run(self):
+        if self.proc is None:
+            return
+        try:
             for line in self.proc.stdout:
                 self.samples.append([x.strip() for x in line.strip().split(",")])
         except Exception:
@@ -73,20 +86,28 @@ class ClockSampler(threading.Thread):
         """Index of the next sample: call at the start and the end of the timed region."""
         return len(self.samples)
 
-    def summary(self, lo=0, hi=None):
-        """Median SM clock / throttle reasons over samples[lo:hi] (the timed region; the sampler is
-        started earlier so that nvidia-smi is already running when the region begins)."""
+    def stop(self):
         if self.proc is not None:
             self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
         self.join(timeout=6)
-        window = self.samples[lo:hi] if len(self.samples[lo:hi]) >= 3 else self.samples
-        self.samples = window
-        mhz = sorted(int(s[0]) for s in self.samples if len(s) >= 7 and s[0].isdigit())
+
+    def summary(self, lo=0, hi=None, note=None):
+        """Median SM clock / throttle reasons over samples[lo:hi]; stops the sampler."""
+        self.stop()
+        window = self.samples[lo:hi]
+        mhz = sorted(int(s[0]) for s in window if len(s) >= 7 and s[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples if len(s) >= 7 for n, v in zip(names, s[3:7]) if v == "Active"})
-        mx = max((int(s[1]) for s in self.samples if len(s) >= 7 and s[1].isdigit()), default=0)
-        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else 0, "sm_max_mhz": mx, "reasons": reasons,
-                "samples": len(self.samples)}
+        reasons = sorted({n for s in window if len(s) >= 7 for n, v in zip(names, s[3:7]) if v == "Active"})
+        mx = max((int(s[1]) for s in window if len(s) >= 7 and s[1].isdigit()), default=0)
+        out = {"sm_mhz": mhz[len(mhz) // 2] if mhz else 0, "sm_max_mhz": mx, "reasons": reasons,
+               "samples": len(window)}
+        if note:
+            out["window"] = note
+        return out
 
 
 def cpu_reference_step(G_sample, T, D, threads, kind="else_branch"):
@@ -159,9 +180,10 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def pcie_floor(dev, nbytes=256 << 20, reps=3):
+def pcie_floor(dev, nbytes=256 << 20, reps=3, chunk=16 << 20):
     """Duplex host<->device copy rate of THIS rank while every other rank does the same (call
-    between barriers): GB/s per direction with H2D and D2H running at once on two streams."""
+    between barriers): GB/s per direction with H2D and D2H running at once on two streams, in
+    copies of `chunk` bytes (the size the streamed e2e pipeline moves per tensor and chunk)."""
     h_a = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
     h_b = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
     d_a = torch.empty(nbytes, dtype=torch.uint8, device=dev)
@@ -169,10 +191,11 @@ def pcie_floor(dev, nbytes=256 << 20, reps=3):
     s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
 
     def both():
-        with torch.cuda.stream(s1):
-            d_a.copy_(h_a, non_blocking=True)
-        with torch.cuda.stream(s2):
-            h_b.copy_(d_b, non_blocking=True)
+        for lo in range(0, nbytes, chunk):
+            with torch.cuda.stream(s1):
+                d_a[lo:lo + chunk].copy_(h_a[lo:lo + chunk], non_blocking=True)
+            with torch.cuda.stream(s2):
+                h_b[lo:lo + chunk].copy_(d_b[lo:lo + chunk], non_blocking=True)
 
     both()
     torch.cuda.synchronize(dev)
@@ -330,7 +353,6 @@ def run_ours(args):
     # ---- timed region: device-resident inputs, CUDA events on the launch stream
     sampler = ClockSampler(local_rank)
     sampler.start()
-    time.sleep(0.3)
     launches0 = native.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     barrier()
@@ -342,7 +364,18 @@ def run_ours(args):
     barrier()
     m1 = sampler.mark()
     launches = native.launch_count() - launches0
-    clocks = sampler.summary(m0, m1)
+    note = "timed region"
+    if m1 - m0 < 3:
+        # the region is shorter than three 20 ms sampling periods: sample an UNTIMED repeat of the
+        # same loop (same kernels, same load) for ~0.3 s and say so
+        m0 = sampler.mark()
+        t_rep = time.perf_counter()
+        while time.perf_counter() - t_rep < 0.3:
+            step()
+            torch.cuda.synchronize()
+        m1 = sampler.mark()
+        note = "untimed repeat of the timed loop (the timed region lasted less than 3 sampling periods)"
+    clocks = sampler.summary(m0, m1, note)
     ms_step = max_over_ranks(ev[0].elapsed_time(ev[1])) / args.steps
     value = flops_global / (ms_step * 1e-3) / 1e12
 

@@ -3,7 +3,8 @@ import sys, torch
 sys.path.insert(0, ".")
 import flash_attention_ipu_b200.streaming as st
 from flash_attention_ipu_b200.streaming import HostStreamedAttention
-G, T, D, gc = 128, 8192, 128, 8
+import os
+G, T, D, gc = int(os.environ.get("E2E_G", "128")), 8192, 128, 8
 h_qkv = torch.randn(3, G, T, D).bfloat16().pin_memory()
 h_do = torch.randn(G, T, D).bfloat16().pin_memory()
 h_out = torch.empty(G, T, D, dtype=torch.bfloat16).pin_memory()
@@ -12,7 +13,7 @@ marks = []
 def ev(stream, tag):
     e = torch.cuda.Event(enable_timing=True); e.record(stream); marks.append((tag, e))
 class Traced(HostStreamedAttention):
-    def run(self, h_qkv, h_dout, h_out, h_dqkv):
+    def run(self, h_qkv, h_dout, h_out, h_dqkv, sync=False):
         cur = torch.cuda.current_stream(self.dev)
         gc = self.gc
         for c in range(self.n + 1):
@@ -55,5 +56,10 @@ t0 = marks[0][1]
 rows = {}
 for tag, e in marks:
     rows.setdefault(tag[:-1], {})[tag[-1]] = t0.elapsed_time(e)
+tag = os.environ.get("E2E_TAG", "")
 for k, v in rows.items():
-    print(f"{k:6s} {v['+']:8.2f} -> {v['-']:8.2f}  ({v['-'] - v['+']:.2f} ms)")
+    print(f"{tag}{k:6s} {v['+']:8.2f} -> {v['-']:8.2f}  ({v['-'] - v['+']:.2f} ms)")
+import time
+t = time.perf_counter()
+for _ in range(5): pipe.run(h_qkv, h_do, h_out, h_dqkv); torch.cuda.synchronize()
+print(f"{tag}step wall {(time.perf_counter() - t) / 5 * 1e3:.2f} ms for G={G}")
