@@ -1,9 +1,10 @@
 #!/bin/bash
 # plain run first (must exit 0), then the ncu launch list and one --set full capture per hot kernel
+# (B200_PROFILING.md recipe).  Reports land in gpurun_out/ and are read back with `ncu -i`.
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-small"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
-ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:fa_fwd_sm100 -s 3 -c 1 -o gpurun_out/prof_fwd -f $CMD > gpurun_out/ncu_fwd.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:fa_bwd_sm100 -s 3 -c 1 -o gpurun_out/prof_bwd -f $CMD > gpurun_out/ncu_bwd.log 2>&1
-ls -la gpurun_out | tail -12
+ls -la gpurun_out | grep -E "prof_|launches"
