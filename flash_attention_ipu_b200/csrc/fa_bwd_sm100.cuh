@@ -40,6 +40,10 @@
 #include <type_traits>
 #include "fa_fwd_sm100.cuh"
 
+#if defined(FA_EXPERIMENT_NO_REDUCE) && !defined(FA_ALLOW_EXPERIMENTS)
+#error "FA_EXPERIMENT_* builds remove work and give wrong results: define FA_ALLOW_EXPERIMENTS to build one on purpose"
+#endif
+
 namespace fa {
 
 constexpr int kBwdThreads = 512;
@@ -402,7 +406,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
+#ifndef FA_EXPERIMENT_NO_REDUCE  // timing / power experiment only when defined (wrong results; needs FA_ALLOW_EXPERIMENTS)
             tma_reduce_add_4d(&tmDQ, slab, c * 32, i * 128 + wq * 32, h, t.b);
+#endif
             tma_store_commit();
           }
         }
