@@ -32,3 +32,11 @@ _lib, _lib_path = _load_native_library()
 
 from ._impl.flash_attention_qkv_packed import *  # noqa: E402,F401,F403
 from ._impl.flash_attention_qkv_packed import __all__  # noqa: E402,F401
+
+
+def set_deterministic(on: bool) -> bool:
+    """Bit-reproducible gradients: dQ partials are added in a fixed order (``fa_b200_set_deterministic``)
+    for every later backward of this process, at a throughput cost.  Returns the previous setting.
+    ``torch.use_deterministic_algorithms(True)`` selects the same mode for the torch ops."""
+    from ._impl import native
+    return native.set_deterministic(on)

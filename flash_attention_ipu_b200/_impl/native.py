@@ -18,7 +18,7 @@ EXPORTED_SYMBOLS = (
     "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_dq_accum", "fa_b200_bwd_sm_clock",
     "fa_b200_merge",
     "fa_b200_merge_acc",
-    "fa_b200_kernel_family", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
+    "fa_b200_kernel_family", "fa_b200_set_deterministic", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
     "fa_b200_version",
 )
 
@@ -52,6 +52,8 @@ _lib.fa_b200_merge.restype = c_int
 _lib.fa_b200_merge_acc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                                    c_int32, c_int32, c_void_p]
 _lib.fa_b200_merge_acc.restype = c_int
+_lib.fa_b200_set_deterministic.argtypes = [c_int]
+_lib.fa_b200_set_deterministic.restype = c_int
 _lib.fa_b200_kernel_family.argtypes = [_PP]
 _lib.fa_b200_kernel_family.restype = c_int
 _lib.fa_b200_launch_count.argtypes = []
@@ -77,6 +79,12 @@ def tmap_cache_stats() -> tuple:
     hits, misses = c_int64(0), c_int64(0)
     _lib.fa_b200_tmap_cache_stats(byref(hits), byref(misses))
     return int(hits.value), int(misses.value)
+
+
+def set_deterministic(on: bool) -> bool:
+    """Ordered (bit-reproducible) dQ accumulation for every later tensor-family backward of this
+    process; returns the previous setting."""
+    return bool(_lib.fa_b200_set_deterministic(int(bool(on))))
 
 
 def version() -> int:

@@ -19,6 +19,7 @@ namespace {
 
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
+std::atomic<int> g_deterministic{0};  // fa_b200_set_deterministic
 
 int fail(int code, const char *fmt, ...) {
   va_list ap;
@@ -393,6 +394,9 @@ size_t ws_stat_bytes(const fa_b200_problem *p) {
   return align256((size_t)p->B * p->H * lq_pad(p) * sizeof(float));
 }
 size_t ws_acc_bytes(const fa_b200_problem *p) { return align256((size_t)p->B * p->H * p->Lq * p->D * sizeof(float)); }
+// deterministic dQ: one counter per (group, Q tile, drain warp)
+size_t ws_sem_count(const fa_b200_problem *p) { return (size_t)p->B * p->H * ((p->Lq + 127) / 128) * 4; }
+size_t ws_sem_bytes(const fa_b200_problem *p) { return align256(ws_sem_count(p) * sizeof(int)); }
 
 template <int D, bool kBf16>
 int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
@@ -407,11 +411,12 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   float *lse2 = reinterpret_cast<float *>(ws + ws_stat_bytes(p));
   float *dq_acc = reinterpret_cast<float *>(ws + 2 * ws_stat_bytes(p));
   int *counter = reinterpret_cast<int *>(ws + 2 * ws_stat_bytes(p) + ws_acc_bytes(p));
+  int *dq_sem = g_deterministic.load(std::memory_order_relaxed) ? reinterpret_cast<int *>(ws + 2 * ws_stat_bytes(p) + ws_acc_bytes(p) + 256) : nullptr;
   const int G = p->B * p->H, Lp = lq_pad(p);
   fa::fa_bwd_prep_kernel<T, D><<<blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st>>>(
       reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
       reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
-      delta, lse2, dq_accum ? nullptr : dq_acc, p->B, p->H, p->Lq, Lp, counter);
+      delta, lse2, dq_accum ? nullptr : dq_acc, p->B, p->H, p->Lq, Lp, counter, dq_sem, (int)ws_sem_count(p));
   if (int rc = launched()) return rc;
 
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
@@ -425,7 +430,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
-  bp.lse2 = lse2; bp.delta = delta; bp.sched_counter = counter;
+  bp.lse2 = lse2; bp.delta = delta; bp.sched_counter = counter; bp.dq_sem = dq_sem;
   bp.clock_out = reinterpret_cast<unsigned long long *>(counter + 2);  // 8-byte aligned, inside the counter's 256-byte slot
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
   bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;
@@ -472,7 +477,8 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
 extern "C" {
 
 const char *fa_b200_last_error(void) { return g_err; }
-int fa_b200_version(void) { return 100; }
+int fa_b200_version(void) { return 200; }
+int fa_b200_set_deterministic(int on) { return g_deterministic.exchange(on ? 1 : 0, std::memory_order_relaxed); }
 int64_t fa_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 void fa_b200_tmap_cache_stats(int64_t *hits, int64_t *misses) {
   if (hits) *hits = g_tmap_hits.load(std::memory_order_relaxed);
@@ -516,7 +522,7 @@ int fa_b200_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 size_t fa_b200_bwd_workspace_bytes(const fa_b200_problem *p) {
   if (!p || p->B <= 0 || p->H <= 0 || p->Lq <= 0 || p->D <= 0) return 0;
   if (family(p) == 1)
-    return 2 * ws_stat_bytes(p) + ws_acc_bytes(p) + 256;
+    return 2 * ws_stat_bytes(p) + ws_acc_bytes(p) + 256 + ws_sem_bytes(p);
   return align256((size_t)p->B * p->H * p->Lq * sizeof(float));  // delta[G][Lq]
 }
 

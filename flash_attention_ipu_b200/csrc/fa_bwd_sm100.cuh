@@ -59,6 +59,9 @@ struct BwdParams {
   const float *delta;  // [G][Lq_pad]  -rowsum(O o dO); 0 for padding
   int *sched_counter;  // zeroed by fa_bwd_prep_kernel; next unclaimed item = gridDim.x + counter
   unsigned long long *clock_out;  // [2]: SM cycles and nanoseconds CTA 0 spent in the kernel (effective SM clock under load)
+  // deterministic dQ (fa_b200_set_deterministic): dq_sem[(group * num_q_tiles + i) * 4 + drain warp] counts the KV
+  // tiles whose partial of Q tile i has been reduce-added; zeroed by fa_bwd_prep_kernel.  nullptr: arrival order.
+  int *dq_sem;
   int Lq, Lk, H, Lq_pad;
   int Hkv, kv_ratio;   // K/V heads and query heads per K/V head (H = Hkv * kv_ratio; 1 = multi-head)
   int causal, shift;
@@ -106,7 +109,11 @@ template <bool kGqa>
 __device__ __forceinline__ BwdItem bwd_decode(const BwdParams &p, int w, int num_q_tiles) {
   BwdItem t;
   const int gk = w / p.num_kv_tiles;
-  t.j = w % p.num_kv_tiles;  // ascending: the KV tiles with most Q tiles first
+  // ascending: the KV tiles with most Q tiles first.  Deterministic dQ: DESCENDING, because the
+  // partials of a Q tile are then added in descending KV-tile order and the tile a CTA waits for
+  // must have been claimed before its own (it is then running or done: no deadlock, and it reaches
+  // every shared Q tile one iteration earlier, so the wait is normally already satisfied)
+  t.j = p.dq_sem ? p.num_kv_tiles - 1 - (w % p.num_kv_tiles) : w % p.num_kv_tiles;
   t.b = gk / p.Hkv;
   t.hk = gk % p.Hkv;
   t.i0 = bwd_first_q_tile(p, t.j);
@@ -214,8 +221,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_arrive(&sched_full[s]);
         if (w >= p.num_items) break;
         const BwdItem t = bwd_decode<kGqa>(p, w, num_q_tiles);
-        // claim the following item now, and pull its K / V tiles into L2 while this one runs
-        const int w_next = gridDim.x + atomicAdd(p.sched_counter, 1);
+        // claim the following item now, and pull its K / V tiles into L2 while this one runs.
+        // Deterministic dQ claims only when this item is done: CTAs wait for the KV tile claimed
+        // just before theirs, so a claimed item must be one that is being worked on.
+        int w_next = p.dq_sem ? p.num_items : gridDim.x + atomicAdd(p.sched_counter, 1);
         if (w_next < p.num_items) {
           const BwdItem tn = bwd_decode<kGqa>(p, w_next, num_q_tiles);
           if (tn.n > 0)
@@ -251,6 +260,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
         }
         if (t.n > 0) ++kc;
+        if (p.dq_sem) w_next = gridDim.x + atomicAdd(p.sched_counter, 1);
         w = w_next;
       }
     }
@@ -393,6 +403,19 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive_warp(dq_empty);  // dQ has left TMEM: nothing below is on the tensor pipe's path
+        int *sem = nullptr;
+        if (p.dq_sem) {
+          // ordered accumulation: wait until every KV tile above this one that sees Q tile i has added
+          // its partial of these 32 rows.  j_max = last KV tile with bwd_first_q_tile(j) <= i.
+          int j_max = p.num_kv_tiles - 1;
+          if (p.causal) j_max = min(j_max, (i * 128 + 127 + p.shift) / 128);
+          sem = p.dq_sem + ((static_cast<size_t>(t.b * p.H + h) * num_q_tiles + i) * 4 + wq);
+          if (lane == 0) {
+            const int want = j_max - t.j;
+            while (ld_acquire_gpu(sem) < want) { }
+          }
+          __syncwarp();
+        }
         #pragma unroll
         for (int c = 0; c < kSlabs; ++c) {
           uint8_t *slab = wstage + (c % L::kDrainSlabs) * L::kSlabBytes;
@@ -411,6 +434,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #endif
             tma_store_commit();
           }
+        }
+        if (sem != nullptr && lane == 0) {
+          tma_store_wait<0>();       // the reduce-adds have been PERFORMED, not merely read from the slabs
+          red_release_gpu_add(sem, 1);
         }
       }
     }
@@ -621,9 +648,13 @@ template <typename T, int D>
 __global__ void __launch_bounds__(256)
 fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T *dout, int64_t d_sb,
                    int64_t d_sh, int64_t d_sl, const float *lse, float *delta, float *lse2,
-                   float *dq_acc, int B, int H, int Lq, int Lq_pad, int *sched_counter) {
+                   float *dq_acc, int B, int H, int Lq, int Lq_pad, int *sched_counter, int *dq_sem, int sem_count) {
   constexpr int kTpr = D / 8;  // threads per row
   if (blockIdx.x == 0 && threadIdx.x == 0) *sched_counter = 0;
+  if (dq_sem)
+    for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < sem_count;
+         e += static_cast<int64_t>(gridDim.x) * blockDim.x)
+      dq_sem[e] = 0;
   const int sub = threadIdx.x % kTpr;
   const int64_t rid = static_cast<int64_t>(blockIdx.x) * (256 / kTpr) + threadIdx.x / kTpr;
   const bool in_range = rid < static_cast<int64_t>(B) * H * Lq_pad;

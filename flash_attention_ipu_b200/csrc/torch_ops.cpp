@@ -130,9 +130,13 @@ void run_bwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const T
   const Tensor ws = at::empty({ws_bytes}, q.options().dtype(at::kByte));
   const fa_b200_tensor tq = desc(q), tk = desc(k), tv = desc(v), to = desc(o), tdo = desc(dout);
   const fa_b200_tensor tdq = desc(dq), tdk = desc(dk), tdv = desc(dv);
-  check(fa_b200_bwd(&p, &tq, &tk, &tv, &to, &tdo, lse.data_ptr<float>(), &tdq, &tdk, &tdv, ws.data_ptr(),
-                    static_cast<size_t>(ws_bytes), c10::cuda::getCurrentCUDAStream(q.device().index()).stream()),
-        "fa_b200_bwd");
+  // torch.use_deterministic_algorithms(True) asks for the ordered dQ accumulation for this call
+  const bool det = at::globalContext().deterministicAlgorithms();
+  const int prev = det ? fa_b200_set_deterministic(1) : 0;
+  const int rc = fa_b200_bwd(&p, &tq, &tk, &tv, &to, &tdo, lse.data_ptr<float>(), &tdq, &tdk, &tdv, ws.data_ptr(),
+                             static_cast<size_t>(ws_bytes), c10::cuda::getCurrentCUDAStream(q.device().index()).stream());
+  if (det) fa_b200_set_deterministic(prev);
+  check(rc, "fa_b200_bwd");
 }
 
 // ------------------------------------------------------------------ separate q, k, v (SDPA path)

@@ -117,6 +117,13 @@ int fa_b200_merge_acc(float *o_acc, float *lse_acc, const void *o_b, const float
                       int64_t n_outer, int64_t n_inner, int64_t acc_outer_stride, int64_t acc_row0,
                       int32_t D, int32_t dtype_b, void *stream);
 
+/* Deterministic gradients.  dQ tiles are accumulated across KV tiles by fp32 reduce-adds; by default
+ * in arrival order (run-to-run differences ~1e-7 relative).  With on != 0 every later tensor-family
+ * backward adds the partials of a Q tile in a fixed (descending KV tile) order behind per-tile
+ * semaphores: bit-identical results from run to run, at a throughput cost.  Process-wide; returns
+ * the previous setting.  (dK, dV and the forward are deterministic either way.) */
+int fa_b200_set_deterministic(int on);
+
 /* Which kernel family a problem dispatches to: 1 = tcgen05/TMA sm_100a kernels,
  * 0 = generic SIMT kernels (fp32 inputs / head dims the tensor path does not cover),
  * negative = unsupported. */
