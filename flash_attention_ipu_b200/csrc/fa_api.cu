@@ -112,34 +112,49 @@ struct TmapKey {
   const void *ptr;
   int64_t sb, sh, sl;
   int32_t dtype, B, H, L, D, box_rows;
+  bool operator==(const TmapKey &o) const {
+    return ptr == o.ptr && sb == o.sb && sh == o.sh && sl == o.sl && dtype == o.dtype && B == o.B && H == o.H &&
+           L == o.L && D == o.D && box_rows == o.box_rows;
+  }
 };
 struct TmapSlot {
   TmapKey key;
   CUtensorMap map;
+  bool used;
 };
-constexpr int kTmapSlots = 64;
+// Direct-mapped with 4-way sets: a lookup hashes the key and scans one set of 4 slots (the 64-slot
+// linear scan of round 1 was visible at GPT-2 size, where host time is the bound, and the streamed
+// e2e path allocates fresh outputs per chunk, i.e. misses and evicts by construction).
+constexpr int kTmapSets = 256, kTmapWays = 4;
 std::mutex g_tmap_mu;
-TmapSlot g_tmap[kTmapSlots];
-int g_tmap_used = 0, g_tmap_next = 0;
+TmapSlot g_tmap[kTmapSets][kTmapWays];
+unsigned g_tmap_victim[kTmapSets];
 std::atomic<int64_t> g_tmap_hits{0}, g_tmap_misses{0};
 
+unsigned tmap_set(const TmapKey &k) {
+  uint64_t h = reinterpret_cast<uintptr_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+  h ^= (uint64_t)k.sl * 0xC2B2AE3D27D4EB4Full + (uint64_t)k.L * 0x165667B19E3779F9ull + (uint64_t)k.box_rows * 0x27D4EB2F165667C5ull;
+  return (unsigned)(h >> 40) % kTmapSets;
+}
 bool tmap_lookup(const TmapKey &k, CUtensorMap *m) {
+  const unsigned s = tmap_set(k);
   std::lock_guard<std::mutex> lock(g_tmap_mu);
-  for (int i = 0; i < g_tmap_used; ++i) {
-    const TmapKey &c = g_tmap[i].key;
-    if (c.ptr == k.ptr && c.sb == k.sb && c.sh == k.sh && c.sl == k.sl && c.dtype == k.dtype && c.B == k.B &&
-        c.H == k.H && c.L == k.L && c.D == k.D && c.box_rows == k.box_rows) {
-      *m = g_tmap[i].map;
+  for (int w = 0; w < kTmapWays; ++w)
+    if (g_tmap[s][w].used && g_tmap[s][w].key == k) {
+      *m = g_tmap[s][w].map;
       return true;
     }
-  }
   return false;
 }
 void tmap_insert(const TmapKey &k, const CUtensorMap &m) {
+  const unsigned s = tmap_set(k);
   std::lock_guard<std::mutex> lock(g_tmap_mu);
-  const int i = g_tmap_used < kTmapSlots ? g_tmap_used++ : (g_tmap_next++ % kTmapSlots);  // round-robin eviction
-  g_tmap[i].key = k;
-  g_tmap[i].map = m;
+  int w = 0;
+  for (; w < kTmapWays && g_tmap[s][w].used; ++w) { }
+  if (w == kTmapWays) w = g_tmap_victim[s]++ % kTmapWays;  // round-robin eviction inside the set
+  g_tmap[s][w].key = k;
+  g_tmap[s][w].map = m;
+  g_tmap[s][w].used = true;
 }
 
 // (B,H,L,D) tensor, box = 128 bytes of D x `box_rows` rows, 128B swizzle.
