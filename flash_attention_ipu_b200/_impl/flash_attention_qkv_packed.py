@@ -19,7 +19,7 @@ from . import ops
 
 def flash_attention_qkv_packed(
     qkv: torch.Tensor, num_chunks_q: int, num_chunks_kv: int, *, causal: bool = True,
-    softmax_scale: float = 1.0
+    softmax_scale: float = 1.0, kv_lens: "torch.Tensor | None" = None
 ) -> torch.Tensor:
     """
     Memory-efficient causally masked multi-head attention from a packed qkv tensor
@@ -28,6 +28,10 @@ def flash_attention_qkv_packed(
 
     qkv -- shape (3, N, L, D)
     returns -- shape (N, L, D)
+
+    Keyword extensions of the B200 build (the reference has none of them): ``causal=False``,
+    ``softmax_scale``, and ``kv_lens`` -- an int32 CUDA tensor with one entry per group n: only the
+    first ``kv_lens[n]`` keys / values of group n exist, the rest is padding (its dk, dv are zero).
     """
     if qkv.ndim != 4:
         raise ValueError("flash_attention_qkv_packed expects qkv input to have 4 dimensions")
@@ -48,7 +52,7 @@ def flash_attention_qkv_packed(
         )
     L = qkv.shape[2]
     out, _lse = ops.qkv_packed_fwd(qkv, float(softmax_scale), bool(causal),
-                                   L // num_chunks_q, L // num_chunks_kv)
+                                   L // num_chunks_q, L // num_chunks_kv, kv_lens)
     return out
 
 

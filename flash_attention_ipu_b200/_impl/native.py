@@ -32,7 +32,7 @@ class Problem(Structure):  # fa_b200_problem
         ("B", c_int32), ("H", c_int32), ("Lq", c_int32), ("Lk", c_int32), ("D", c_int32),
         ("dtype", c_int32), ("causal", c_int32), ("softmax_scale", c_float),
         ("block_q_hint", c_int32), ("block_kv_hint", c_int32), ("q_pos0", c_int32), ("kv_pos0", c_int32),
-        ("H_kv", c_int32),
+        ("H_kv", c_int32), ("kv_lens", c_void_p),
     ]
 
 
@@ -111,15 +111,21 @@ def _require_cuda(*ts: torch.Tensor) -> None:
 
 
 def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
-                 block_q: int = 0, block_kv: int = 0, q_pos0: int = 0, kv_pos0: int = 0) -> Problem:
+                 block_q: int = 0, block_kv: int = 0, q_pos0: int = 0, kv_pos0: int = 0,
+                 kv_lens: "torch.Tensor | None" = None) -> Problem:
     if q.dtype not in _DTYPES:
         raise RuntimeError(f"unsupported dtype {q.dtype}")
     B, H, Lq, D = q.shape
     H_kv = k.shape[1]  # fewer K/V heads than query heads = grouped-query attention
     if H % H_kv:
         raise RuntimeError(f"{H} query heads are not a multiple of {H_kv} key/value heads")
+    lens_ptr = None
+    if kv_lens is not None:  # the caller keeps the tensor alive until the launches that use the problem are enqueued
+        if not (kv_lens.is_cuda and kv_lens.dtype == torch.int32 and kv_lens.is_contiguous() and kv_lens.numel() == B * H):
+            raise RuntimeError("kv_lens must be a contiguous CUDA int32 tensor with B*H entries")
+        lens_ptr = kv_lens.data_ptr()
     return Problem(B, H, Lq, k.shape[2], D, _DTYPES[q.dtype], int(bool(causal)), float(scale),
-                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv)
+                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv, lens_ptr)
 
 
 def kernel_family(prob: Problem) -> int:

@@ -28,6 +28,26 @@ def _chunk_heuristic(L: int, D: int):
     return int(2 ** (ceil(log2(r) / 2))), int(2 ** (floor(log2(r) / 2)))
 
 
+def _key_padding_lengths(mask: torch.Tensor, query: torch.Tensor, key: torch.Tensor):
+    """(B*H,) int32 key counts of a boolean key-padding mask, or None if `mask` is not of that form
+    or the problem is off the tensor path."""
+    if (mask.dtype != torch.bool or query.ndim != 4 or not query.is_cuda or not mask.is_cuda
+            or query.dtype not in (torch.bfloat16, torch.float16) or query.shape[-1] not in (64, 128)):
+        return None
+    B, H, Lk = query.shape[0], query.shape[1], key.shape[-2]
+    if mask.shape == (B, Lk):
+        rows = mask
+    elif mask.shape == (B, 1, 1, Lk):
+        rows = mask.view(B, Lk)
+    else:
+        return None
+    lens = rows.sum(-1, dtype=torch.int32)
+    ar = torch.arange(Lk, device=mask.device, dtype=torch.int32)
+    torch._assert_async((rows == (ar[None, :] < lens[:, None])).all(),
+                        "attn_mask is not a key-padding mask (True entries must be a prefix of every row)")
+    return lens.repeat_interleave(H).contiguous()
+
+
 def _sdpa_impl(
     orig_fn: Callable,
     query: torch.Tensor,
@@ -39,8 +59,17 @@ def _sdpa_impl(
     scale: Optional[float] = None,
     enable_gqa: bool = False,
 ) -> torch.Tensor:
+    kv_lens = None
     if attn_mask is not None:
-        raise NotImplementedError("flash_attention_ipu does not currently support passing attn_mask")
+        # The reference refuses every mask (:21-24).  Here ONE form is taken: a boolean key-padding
+        # mask, (B, 1, 1, Lk) or (B, Lk) shaped, whose True entries are a prefix of each row -- it is
+        # the per-batch number of existing keys (``fa_b200_problem.kv_lens``).  The prefix property is
+        # asserted on the device without a host synchronisation.
+        kv_lens = _key_padding_lengths(attn_mask, query, key)
+        if kv_lens is None:
+            raise NotImplementedError(
+                "flash_attention_ipu supports attn_mask only as a boolean key-padding mask of shape "
+                "(B, 1, 1, Lk) whose True entries form a prefix of every row (bf16 / fp16, D in {64, 128})")
     if dropout_p > 0.0:
         raise NotImplementedError("flash_attention_ipu does not currently support non-zero dropout_p")
     gqa = (enable_gqa and query.ndim == 4 and key.ndim == 4 and key.shape == value.shape
@@ -77,7 +106,7 @@ def _sdpa_impl(
     else:
         q, k, v = (t.reshape(1, -1, L, D) for t in (query, key, value))
     out, _lse = ops.attention_fwd(q, k, v, softmax_scale, bool(is_causal),
-                                  L // num_chunks_q, L // num_chunks_kv)
+                                  L // num_chunks_q, L // num_chunks_kv, kv_lens)
     return out.reshape(*batch_shape, L, D) if query.ndim != 4 else out
 
 

@@ -60,6 +60,8 @@ int check_problem(const fa_b200_problem *p) {
     return fail(FA_B200_ERR_UNSUPPORTED, "grouped-query attention needs the tensor path (16-bit, D in {64,128})");
   if (p->D > fa::kGenMaxD && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
     return fail(FA_B200_ERR_UNSUPPORTED, "head dim %d > %d", p->D, fa::kGenMaxD);
+  if (p->kv_lens && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
+    return fail(FA_B200_ERR_UNSUPPORTED, "kv_lens (key padding) needs the tensor path (16-bit, D in {64,128})");
   // every kernel folds (tiles x groups) into a 1-D grid
   const int64_t lmax = p->Lq > p->Lk ? p->Lq : p->Lk;
   if ((int64_t)p->B * p->H * ((lmax + 63) / 64) > INT32_MAX)
@@ -375,6 +377,7 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tv, v, p->dtype, p->B, kv_heads(p), p->Lk, D, fa::kBlockN)) return rc;
   fa::FwdParams fp;
   fp.lse = lse;
+  fp.kv_lens = p->kv_lens;
   fp.Lq = p->Lq; fp.Lk = p->Lk; fp.H = p->H;
   fp.kv_ratio = p->H / kv_heads(p);
   fp.causal = p->causal;
@@ -445,7 +448,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   if (int rc = make_tmap(&tdk, dk, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   if (int rc = make_tmap(&tdv, dv, p->dtype, p->B, Hkv, p->Lk, D, 128)) return rc;
   fa::BwdParams bp;
-  bp.lse2 = lse2; bp.delta = delta; bp.sched_counter = counter; bp.dq_sem = dq_sem;
+  bp.lse2 = lse2; bp.delta = delta; bp.sched_counter = counter; bp.dq_sem = dq_sem; bp.kv_lens = p->kv_lens;
   bp.clock_out = reinterpret_cast<unsigned long long *>(counter + 2);  // 8-byte aligned, inside the counter's 256-byte slot
   bp.Lq = p->Lq; bp.Lk = p->Lk; bp.H = p->H; bp.Lq_pad = Lp;
   bp.Hkv = Hkv; bp.kv_ratio = p->H / Hkv;

@@ -57,6 +57,7 @@ constexpr int kBwdConsumerWarps = 13;             // compute 8 + drain 4 + MMA 1
 struct BwdParams {
   const float *lse2;   // [G][Lq_pad]  -lse * log2(e); -inf for padding / rows without keys
   const float *delta;  // [G][Lq_pad]  -rowsum(O o dO); 0 for padding
+  const int *kv_lens;  // [B*H] keys of each (batch, query head) that exist (<= Lk), or nullptr
   int *sched_counter;  // zeroed by fa_bwd_prep_kernel; next unclaimed item = gridDim.x + counter
   unsigned long long *clock_out;  // [2]: SM cycles and nanoseconds CTA 0 spent in the kernel (effective SM clock under load)
   // deterministic dQ (fa_b200_set_deterministic): dq_sem[(group * num_q_tiles + i) * 4 + drain warp] counts the KV
@@ -103,7 +104,7 @@ __device__ __forceinline__ int bwd_first_q_tile(const BwdParams &p, int j) {
 // query head that shares the K/V head (grouped-query attention: kv_ratio heads, dK / dV simply keep
 // accumulating in TMEM across them)
 struct BwdItem {
-  int b, hk, j, i0, n, h0;
+  int b, hk, j, i0, n, h0, lk;
 };
 template <bool kGqa>
 __device__ __forceinline__ BwdItem bwd_decode(const BwdParams &p, int w, int num_q_tiles) {
@@ -117,9 +118,12 @@ __device__ __forceinline__ BwdItem bwd_decode(const BwdParams &p, int w, int num
   t.b = gk / p.Hkv;
   t.hk = gk % p.Hkv;
   t.i0 = bwd_first_q_tile(p, t.j);
-  const int n1 = max(num_q_tiles - t.i0, 0);
-  t.n = kGqa ? n1 * p.kv_ratio : n1;
   t.h0 = kGqa ? t.hk * p.kv_ratio : t.hk;
+  // key padding (one length per batch element; stored per (batch, query head)): a KV tile made of
+  // padding only has no Q tile to visit and writes dK = dV = 0
+  t.lk = p.kv_lens ? min(p.Lk, max(__ldg(p.kv_lens + t.b * p.H + t.h0), 0)) : p.Lk;
+  const int n1 = t.j * 128 < t.lk ? max(num_q_tiles - t.i0, 0) : 0;
+  t.n = kGqa ? n1 * p.kv_ratio : n1;
   return t;
 }
 
@@ -407,7 +411,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (p.dq_sem) {
           // ordered accumulation: wait until every KV tile above this one that sees Q tile i has added
           // its partial of these 32 rows.  j_max = last KV tile with bwd_first_q_tile(j) <= i.
-          int j_max = p.num_kv_tiles - 1;
+          int j_max = (t.lk + 127) / 128 - 1;  // KV tiles made of padding only add nothing
           if (p.causal) j_max = min(j_max, (i * 128 + 127 + p.shift) / 128);
           sem = p.dq_sem + ((static_cast<size_t>(t.b * p.H + h) * num_q_tiles + i) * 4 + wq);
           if (lane == 0) {
@@ -512,7 +516,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         // S = 0 and exp2(-lse2) is unbounded for rows with a strongly negative LSE.  Select, not
         // multiply: the value may be inf / polynomial garbage.  (The forward masks the same keys
         // through `limit = Lk - 1 - col0`.)
-        if (t.j * 128 + 128 > p.Lk && key >= p.Lk) {
+        if (t.j * 128 + 128 > t.lk && key >= t.lk) {
           #pragma unroll
           for (int c = 0; c < 64; ++c) pr[c] = 0.f;
         }

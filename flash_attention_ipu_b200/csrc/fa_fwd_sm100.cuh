@@ -68,6 +68,7 @@ constexpr int kFwdConsumerWarps = 9;       // 8 softmax warps + the MMA warp rea
 
 struct FwdParams {
   float *lse;         // [G][Lq] fp32
+  const int *kv_lens; // [B*H] keys of each (batch, head) that exist (<= Lk; the rest is padding), or nullptr
   int *sched_counter; // zeroed before the launch; next unclaimed item = gridDim.x + counter.  nullptr: grid = items
   int Lq, Lk, H;      // H: heads per batch (group g -> (b = g / H, h = g % H))
   int kv_ratio;       // query heads per K/V head (1 = multi-head; >1 = grouped-query attention)
@@ -93,10 +94,10 @@ struct FwdSmem {
   static constexpr int kAlloc = kBytes;  // the dynamic shared memory base is 1024-byte aligned (checked)
 };
 
-// number of KV tiles Q tile `t` must visit
-__device__ __forceinline__ int fwd_num_kv_tiles(const FwdParams &p, int t) {
+// number of KV tiles Q tile `t` must visit; `lk` = keys of this group that exist
+__device__ __forceinline__ int fwd_num_kv_tiles(const FwdParams &p, int t, int lk) {
   if (t * kBlockM >= p.Lq) return 0;
-  int hi = p.Lk;  // exclusive bound on visible key index
+  int hi = lk;  // exclusive bound on visible key index
   if (p.causal) {
     int last_row = min(t * kBlockM + kBlockM, p.Lq) - 1;
     hi = min(hi, last_row + p.shift + 1);
@@ -107,7 +108,7 @@ __device__ __forceinline__ int fwd_num_kv_tiles(const FwdParams &p, int t) {
 // one work item: Q tiles t0, t0 + 1 of group g; consecutive items share a (batch, head) so K/V stay
 // in L2, and within a group the pairs with most KV tiles come first
 struct FwdItem {
-  int g, b, h, t0, n0, n1, n_max;
+  int g, b, h, t0, n0, n1, n_max, lk;
 };
 __device__ __forceinline__ FwdItem fwd_decode(const FwdParams &p, int w) {
   FwdItem t;
@@ -116,8 +117,9 @@ __device__ __forceinline__ FwdItem fwd_decode(const FwdParams &p, int w) {
   t.b = t.g / p.H;
   t.h = t.g % p.H;
   t.t0 = 2 * pair;
-  t.n0 = fwd_num_kv_tiles(p, t.t0);
-  t.n1 = fwd_num_kv_tiles(p, t.t0 + 1);
+  t.lk = p.kv_lens ? min(p.Lk, max(__ldg(p.kv_lens + t.g), 0)) : p.Lk;  // key-padding: trailing keys do not exist
+  t.n0 = fwd_num_kv_tiles(p, t.t0, t.lk);
+  t.n1 = fwd_num_kv_tiles(p, t.t0 + 1, t.lk);
   t.n_max = max(t.n0, t.n1);
   return t;
 }
@@ -339,9 +341,9 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         // mask (only tiles that cross the causal diagonal or the end of the keys)
         const int col0 = j * kBlockN;
         const bool tile_masked = (p.causal && col0 + kBlockN - 1 > (t.t0 + i) * kBlockM + p.shift) ||
-                                 (col0 + kBlockN > p.Lk);
+                                 (col0 + kBlockN > t.lk);
         if (tile_masked) {
-          int limit = p.Lk - 1 - col0;
+          int limit = t.lk - 1 - col0;
           if (p.causal) limit = min(limit, row + p.shift - col0);
           #pragma unroll
           for (int c = 0; c < 4; ++c)

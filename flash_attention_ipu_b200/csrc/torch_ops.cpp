@@ -18,6 +18,7 @@
 #include <torch/csrc/autograd/custom_function.h>
 #include <torch/library.h>
 
+#include <optional>
 #include <tuple>
 #include <vector>
 
@@ -88,8 +89,19 @@ void check_operands(const Tensor &q, const Tensor &k, const Tensor &v, const Ten
   }
 }
 
+// kv_lens: optional int32 CUDA tensor with one entry per (batch, query head) group -- the keys of that
+// group that exist (key padding).  Returned contiguous so that the caller keeps it alive over the launch.
+Tensor lens_or_empty(const std::optional<Tensor> &kv_lens, const Tensor &q) {
+  if (!kv_lens.has_value() || !kv_lens->defined()) return Tensor();
+  TORCH_CHECK(kv_lens->is_cuda() && kv_lens->device() == q.device(), "kv_lens must be on q's device");
+  TORCH_CHECK(kv_lens->scalar_type() == at::kInt, "kv_lens must be int32");
+  TORCH_CHECK(kv_lens->numel() == q.size(0) * q.size(1), "kv_lens has ", kv_lens->numel(),
+              " entries, expected one per (batch, head) group = ", q.size(0) * q.size(1));
+  return kv_lens->contiguous();
+}
+
 fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, double scale, int64_t block_q,
-                             int64_t block_kv) {
+                             int64_t block_kv, const Tensor &lens = Tensor()) {
   TORCH_CHECK(q.dim() == 4 && k.dim() == 4, "expected (B, H, L, D) operands");
   const int64_t H = q.size(1), Hkv = k.size(1);
   TORCH_CHECK(Hkv > 0 && H % Hkv == 0, H, " query heads are not a multiple of ", Hkv, " key/value heads");
@@ -107,6 +119,7 @@ fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, doub
   p.q_pos0 = 0;
   p.kv_pos0 = 0;
   p.H_kv = Hkv == H ? 0 : static_cast<int32_t>(Hkv);
+  p.kv_lens = lens.defined() ? lens.data_ptr<int32_t>() : nullptr;
   return p;
 }
 
@@ -141,45 +154,51 @@ void run_bwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const T
 
 // ------------------------------------------------------------------ separate q, k, v (SDPA path)
 std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, const Tensor &v_, double scale,
-                                         bool causal, int64_t block_q, int64_t block_kv) {
+                                         bool causal, int64_t block_q, int64_t block_kv,
+                                         const std::optional<Tensor> &kv_lens) {
   require_cuda({&q_, &k_, &v_});
   check_operands(q_, k_, v_, nullptr, nullptr, nullptr);
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_);
   Tensor out = at::empty_like(q);  // keeps q's (possibly (B,L,H,D)-transposed) dense layout
   if (out.stride(-1) != 1) out = at::empty(q.sizes(), q.options());
   const Tensor lse = at::empty({q.size(0), q.size(1), q.size(2)}, q.options().dtype(at::kFloat));
-  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out, lse);
+  const Tensor lens = lens_or_empty(kv_lens, q);
+  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out, lse);
   return {out, lse};
 }
 
 std::tuple<Tensor, Tensor, Tensor> attention_bwd(const Tensor &dout_, const Tensor &q_, const Tensor &k_,
                                                  const Tensor &v_, const Tensor &out_, const Tensor &lse_,
-                                                 double scale, bool causal, int64_t block_q, int64_t block_kv) {
+                                                 double scale, bool causal, int64_t block_q, int64_t block_kv,
+                                                 const std::optional<Tensor> &kv_lens) {
   require_cuda({&dout_, &q_, &k_, &v_, &out_, &lse_});
   check_operands(q_, k_, v_, &out_, &dout_, &lse_);
   const Tensor lse = lse_.contiguous();  // the kernels index it as a dense [B*H][Lq] array
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_), out = as_bhld(out_), dout = as_bhld(dout_);
   const Tensor dq = at::empty_like(q), dk = at::empty_like(k), dv = at::empty_like(v);
-  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out, dout, lse, dq, dk, dv);
+  const Tensor lens = lens_or_empty(kv_lens, q);
+  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out, dout, lse, dq, dk, dv);
   return {dq, dk, dv};
 }
 
 // ------------------------------------------------------------------ packed qkv (reference API)
 // (3,G,L,D) is B=1, H=G with q/k/v = base + {0,1,2}*G*L*D: zero-copy views.
 std::tuple<Tensor, Tensor> qkv_packed_fwd(const Tensor &qkv_, double scale, bool causal, int64_t block_q,
-                                          int64_t block_kv) {
+                                          int64_t block_kv, const std::optional<Tensor> &kv_lens) {
   require_cuda({&qkv_});
   TORCH_CHECK(qkv_.dim() == 4 && qkv_.size(0) == 3, "expected a packed (3, G, L, D) tensor");
   const Tensor qkv = qkv_.contiguous();
   const Tensor q = qkv[0].unsqueeze(0), k = qkv[1].unsqueeze(0), v = qkv[2].unsqueeze(0);
   const Tensor out = at::empty({qkv.size(1), qkv.size(2), qkv.size(3)}, qkv.options());
   const Tensor lse = at::empty({qkv.size(1), qkv.size(2)}, qkv.options().dtype(at::kFloat));
-  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out.unsqueeze(0), lse);
+  const Tensor lens = lens_or_empty(kv_lens, q);
+  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out.unsqueeze(0), lse);
   return {out, lse};
 }
 
 Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out_, const Tensor &lse_,
-                      double scale, bool causal, int64_t block_q, int64_t block_kv) {
+                      double scale, bool causal, int64_t block_q, int64_t block_kv,
+                      const std::optional<Tensor> &kv_lens) {
   require_cuda({&dout_, &qkv_, &out_, &lse_});
   TORCH_CHECK(qkv_.dim() == 4 && qkv_.size(0) == 3, "expected a packed (3, G, L, D) tensor");
   TORCH_CHECK(dout_.dim() == 3 && out_.dim() == 3 && dout_.sizes() == out_.sizes() && out_.size(0) == qkv_.size(1) &&
@@ -191,7 +210,8 @@ Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out
   const Tensor qkv = qkv_.contiguous(), dout = dout_.contiguous(), out = out_.contiguous();
   const Tensor q = qkv[0].unsqueeze(0), k = qkv[1].unsqueeze(0), v = qkv[2].unsqueeze(0);
   const Tensor dqkv = at::empty_like(qkv);  // gradients land directly in the packed buffer
-  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv), q, k, v, out.unsqueeze(0), dout.unsqueeze(0), lse,
+  const Tensor lens = lens_or_empty(kv_lens, q);
+  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out.unsqueeze(0), dout.unsqueeze(0), lse,
           dqkv[0].unsqueeze(0), dqkv[1].unsqueeze(0), dqkv[2].unsqueeze(0));
   return dqkv;
 }
@@ -207,12 +227,14 @@ auto typed_op(const char *name) {
 
 struct AttentionFn : public torch::autograd::Function<AttentionFn> {
   static variable_list forward(AutogradContext *ctx, const Tensor &q, const Tensor &k, const Tensor &v,
-                               double scale, bool causal, int64_t block_q, int64_t block_kv) {
+                               double scale, bool causal, int64_t block_q, int64_t block_kv,
+                               const std::optional<Tensor> &kv_lens) {
     at::AutoDispatchBelowADInplaceOrView below;
     static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, const Tensor &, const Tensor &, double,
-                                                         bool, int64_t, int64_t)>("flash_attention_ipu::attention_fwd");
-    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv);
-    ctx->save_for_backward({q, k, v, out, lse});
+                                                         bool, int64_t, int64_t, const std::optional<Tensor> &)>(
+        "flash_attention_ipu::attention_fwd");
+    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv, kv_lens);
+    ctx->save_for_backward({q, k, v, out, lse, kv_lens.has_value() ? *kv_lens : Tensor()});
     ctx->saved_data["scale"] = scale;
     ctx->saved_data["causal"] = causal;
     ctx->saved_data["block_q"] = block_q;
@@ -223,24 +245,26 @@ struct AttentionFn : public torch::autograd::Function<AttentionFn> {
   static variable_list backward(AutogradContext *ctx, variable_list grads) {
     static auto op = typed_op<std::tuple<Tensor, Tensor, Tensor>(
         const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
-        int64_t, int64_t)>("flash_attention_ipu::attention_bwd");
+        int64_t, int64_t, const std::optional<Tensor> &)>("flash_attention_ipu::attention_bwd");
     const auto saved = ctx->get_saved_variables();
     const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[3]);
+    const std::optional<Tensor> lens = saved[5].defined() ? std::optional<Tensor>(saved[5]) : std::nullopt;
     auto [dq, dk, dv] = op.call(dout, saved[0], saved[1], saved[2], saved[3], saved[4],
                                 ctx->saved_data["scale"].toDouble(), ctx->saved_data["causal"].toBool(),
-                                ctx->saved_data["block_q"].toInt(), ctx->saved_data["block_kv"].toInt());
-    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor()};
+                                ctx->saved_data["block_q"].toInt(), ctx->saved_data["block_kv"].toInt(), lens);
+    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
   }
 };
 
 struct PackedFn : public torch::autograd::Function<PackedFn> {
   static variable_list forward(AutogradContext *ctx, const Tensor &qkv, double scale, bool causal,
-                               int64_t block_q, int64_t block_kv) {
+                               int64_t block_q, int64_t block_kv, const std::optional<Tensor> &kv_lens) {
     at::AutoDispatchBelowADInplaceOrView below;
-    static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, double, bool, int64_t, int64_t)>(
+    static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, double, bool, int64_t, int64_t,
+                                                         const std::optional<Tensor> &)>(
         "flash_attention_ipu::qkv_packed_fwd");
-    auto [out, lse] = op.call(qkv, scale, causal, block_q, block_kv);
-    ctx->save_for_backward({qkv, out, lse});
+    auto [out, lse] = op.call(qkv, scale, causal, block_q, block_kv, kv_lens);
+    ctx->save_for_backward({qkv, out, lse, kv_lens.has_value() ? *kv_lens : Tensor()});
     ctx->saved_data["scale"] = scale;
     ctx->saved_data["causal"] = causal;
     ctx->saved_data["block_q"] = block_q;
@@ -250,39 +274,44 @@ struct PackedFn : public torch::autograd::Function<PackedFn> {
   }
   static variable_list backward(AutogradContext *ctx, variable_list grads) {
     static auto op = typed_op<Tensor(const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
-                                     int64_t, int64_t)>("flash_attention_ipu::qkv_packed_bwd");
+                                     int64_t, int64_t, const std::optional<Tensor> &)>(
+        "flash_attention_ipu::qkv_packed_bwd");
     const auto saved = ctx->get_saved_variables();
     const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[1]);
+    const std::optional<Tensor> lens = saved[3].defined() ? std::optional<Tensor>(saved[3]) : std::nullopt;
     const Tensor dqkv = op.call(dout, saved[0], saved[1], saved[2], ctx->saved_data["scale"].toDouble(),
                                 ctx->saved_data["causal"].toBool(), ctx->saved_data["block_q"].toInt(),
-                                ctx->saved_data["block_kv"].toInt());
-    return {dqkv, Tensor(), Tensor(), Tensor(), Tensor()};
+                                ctx->saved_data["block_kv"].toInt(), lens);
+    return {dqkv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
   }
 };
 
 std::tuple<Tensor, Tensor> attention_fwd_autograd(const Tensor &q, const Tensor &k, const Tensor &v, double scale,
-                                                  bool causal, int64_t block_q, int64_t block_kv) {
-  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv);
+                                                  bool causal, int64_t block_q, int64_t block_kv,
+                                                  const std::optional<Tensor> &kv_lens) {
+  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv, kv_lens);
   return {r[0], r[1]};
 }
 
 std::tuple<Tensor, Tensor> qkv_packed_fwd_autograd(const Tensor &qkv, double scale, bool causal, int64_t block_q,
-                                                   int64_t block_kv) {
-  auto r = PackedFn::apply(qkv, scale, causal, block_q, block_kv);
+                                                   int64_t block_kv, const std::optional<Tensor> &kv_lens) {
+  auto r = PackedFn::apply(qkv, scale, causal, block_q, block_kv, kv_lens);
   return {r[0], r[1]};
 }
 
 }  // namespace
 
 TORCH_LIBRARY(flash_attention_ipu, m) {
+  // kv_lens (optional, int32, one entry per (batch, head) group): key padding -- only the first kv_lens[g]
+  // keys of group g exist.  The reference refuses every attn_mask (_impl/scaled_dot_product_attention.py:21-24).
   m.def("attention_fwd(Tensor q, Tensor k, Tensor v, float softmax_scale, bool causal, int block_q, "
-        "int block_kv) -> (Tensor, Tensor)");
+        "int block_kv, Tensor? kv_lens=None) -> (Tensor, Tensor)");
   m.def("attention_bwd(Tensor dout, Tensor q, Tensor k, Tensor v, Tensor out, Tensor lse, float softmax_scale, "
-        "bool causal, int block_q, int block_kv) -> (Tensor, Tensor, Tensor)");
-  m.def("qkv_packed_fwd(Tensor qkv, float softmax_scale, bool causal, int block_q, int block_kv) -> "
-        "(Tensor, Tensor)");
+        "bool causal, int block_q, int block_kv, Tensor? kv_lens=None) -> (Tensor, Tensor, Tensor)");
+  m.def("qkv_packed_fwd(Tensor qkv, float softmax_scale, bool causal, int block_q, int block_kv, "
+        "Tensor? kv_lens=None) -> (Tensor, Tensor)");
   m.def("qkv_packed_bwd(Tensor dout, Tensor qkv, Tensor out, Tensor lse, float softmax_scale, bool causal, "
-        "int block_q, int block_kv) -> Tensor");
+        "int block_q, int block_kv, Tensor? kv_lens=None) -> Tensor");
 }
 
 // The implementations refuse non-CUDA tensors themselves ("there is no CPU path"), so they are

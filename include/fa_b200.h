@@ -60,6 +60,11 @@ typedef struct {
                          /* multi-query attention (query head h reads K/V head h/(H/H_kv));   */
                          /* k, v, dk, dv are then (B, H_kv, Lk, D).  The reference refuses    */
                          /* this case (_impl/scaled_dot_product_attention.py:33-37).          */
+  const int32_t *kv_lens; /* NULL, or a DEVICE array of B*H ints: group g = b*H+h only has its first  */
+                         /* kv_lens[g] (<= Lk) keys, the rest is padding (the key-padding form of    */
+                         /* attn_mask, which the reference refuses: _impl/scaled_dot_product_        */
+                         /* attention.py:21-24).  All heads of a batch element must agree.  KV tiles  */
+                         /* made of padding are skipped; dK = dV = 0 there.  Tensor path only.        */
 } fa_b200_problem;
 
 /* Forward: replaces flashAttentionQKVPackedWithStash

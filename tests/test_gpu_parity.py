@@ -675,3 +675,78 @@ def test_deterministic_dq_is_bit_reproducible(G, L, D, causal):
     finally:
         torch.use_deterministic_algorithms(False)
     assert torch.equal(again[1], runs[0][1])
+
+
+def _masked_reference(q, k, v, dout, lens, causal, scale):
+    """fp64 attention with a key-padding mask: keys >= lens[b] do not exist."""
+    q, k, v = (t.double().requires_grad_(True) for t in (q, k, v))
+    s = torch.einsum("bhqd,bhkd->bhqk", q, k) * scale
+    Lq, Lk = q.shape[2], k.shape[2]
+    pad = torch.arange(Lk)[None, None, None, :] >= lens.view(-1, 1, 1, 1)
+    s = s.masked_fill(pad, float("-inf"))
+    if causal:
+        s = s.masked_fill(torch.arange(Lk)[None, :] > torch.arange(Lq)[:, None], float("-inf"))
+    out = torch.einsum("bhqk,bhkd->bhqd", torch.softmax(s, dim=-1), v)
+    out.backward(dout.double())
+    return out.detach(), q.grad, k.grad, v.grad
+
+
+@pytest.mark.parametrize("B,H,L,D,causal,lens", [
+    (3, 2, 512, 128, False, [512, 200, 129]),   # BERT-style padding, ragged inside a tile and on a tile edge
+    (2, 4, 384, 64, False, [384, 1]),
+    (2, 2, 512, 128, True, [300, 512]),         # padding on top of the causal mask
+])
+def test_key_padding_mask_via_sdpa(B, H, L, D, causal, lens):
+    """attn_mask as a boolean key-padding mask (the reference refuses every mask,
+    _impl/scaled_dot_product_attention.py:21-24): out and all gradients vs fp64 math; padded keys get
+    dk = dv = 0; a mask that is not a prefix is refused."""
+    import torch.nn.functional as F
+    import flash_attention_ipu_b200._impl.scaled_dot_product_attention as mod
+    native = _native_loaded()
+    torch.manual_seed(SEED + L)
+    q, k, v, dout = (torch.randn(B, H, L, D).bfloat16() for _ in range(4))
+    lens_t = torch.tensor(lens)
+    ref = _masked_reference(q.float(), k.float(), v.float(), dout.float(), lens_t, causal, D ** -0.5)
+    mask = (torch.arange(L)[None, :] < lens_t[:, None]).view(B, 1, 1, L).cuda()
+    qd, kd, vd = (t.cuda().requires_grad_(True) for t in (q, k, v))
+    mod.install()
+    try:
+        before = native.launch_count()
+        out = F.scaled_dot_product_attention(qd, kd, vd, attn_mask=mask, is_causal=causal)
+        out.backward(dout.cuda())
+        torch.cuda.synchronize()
+        assert native.launch_count() > before
+        with pytest.raises(NotImplementedError, match="attn_mask"):   # additive masks stay refused
+            F.scaled_dot_product_attention(qd, kd, vd, attn_mask=torch.zeros(L, L, device="cuda", dtype=torch.bfloat16))
+    finally:
+        mod.uninstall()
+    # causal rows whose visible keys are all real: every row has at least key 0 (lens >= 1)
+    assert (out.detach().float().cpu().double() - ref[0]).abs().max().item() <= 1e-2
+    for got, want in zip((qd.grad, kd.grad, vd.grad), ref[1:]):
+        assert rel_fro(got.float().cpu().double(), want) < 1e-2
+    for b, n in enumerate(lens):
+        assert torch.count_nonzero(kd.grad[b, :, n:]) == 0 and torch.count_nonzero(vd.grad[b, :, n:]) == 0
+
+
+def test_kv_lens_packed_api_and_skipped_tiles():
+    """kv_lens through the packed API: same result as physically truncating K / V, for every group."""
+    import flash_attention_ipu as fa
+    torch.manual_seed(SEED)
+    G, L, D = 3, 640, 128
+    qkv = torch.randn(3, G, L, D, device="cuda", dtype=torch.bfloat16)
+    qkv[0] *= D ** -0.5
+    lens = torch.tensor([640, 257, 128], device="cuda", dtype=torch.int32)
+    x = qkv.clone().requires_grad_(True)
+    out = fa.flash_attention_qkv_packed(x, 1, 1, causal=False, kv_lens=lens)
+    g = torch.randn_like(out)
+    out.backward(g)
+    from flash_attention_ipu_b200._impl import ops
+    for n in range(G):
+        m = int(lens[n])
+        q1, k1, v1 = (qkv[i, n][None, None].clone().requires_grad_(True) for i in range(3))
+        o1, _ = ops.attention_fwd(q1, k1[:, :, :m], v1[:, :, :m], 1.0, False, 0, 0)
+        o1.backward(g[n][None, None])
+        assert torch.equal(o1[0, 0], out[n])
+        assert rel_fro(x.grad[0, n].float(), q1.grad[0, 0].float()) < 1e-5
+        assert torch.equal(x.grad[1, n, :m], k1.grad[0, 0, :m]) and torch.equal(x.grad[2, n, :m], v1.grad[0, 0, :m])
+        assert torch.count_nonzero(x.grad[1:, n, m:]) == 0
