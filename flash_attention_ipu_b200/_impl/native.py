@@ -15,7 +15,7 @@ FA_B200_F16, FA_B200_BF16, FA_B200_F32 = 0, 1, 2
 _DTYPES = {torch.float16: FA_B200_F16, torch.bfloat16: FA_B200_BF16, torch.float32: FA_B200_F32}
 
 EXPORTED_SYMBOLS = (
-    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_dq_accum", "fa_b200_bwd_sm_clock",
+    "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_dq_accum", "fa_b200_bwd_noalloc", "fa_b200_bwd_sm_clock",
     "fa_b200_merge",
     "fa_b200_merge_acc",
     "fa_b200_kernel_family", "fa_b200_set_deterministic", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
@@ -45,6 +45,8 @@ _lib.fa_b200_bwd_workspace_bytes.argtypes = [_PP]
 _lib.fa_b200_bwd_workspace_bytes.restype = c_size_t
 _lib.fa_b200_bwd_dq_accum.argtypes = _lib.fa_b200_bwd.argtypes
 _lib.fa_b200_bwd_dq_accum.restype = c_int
+_lib.fa_b200_bwd_noalloc.argtypes = [_PP, _PT, _PT, _PT, _PT, _PT, c_void_p, _PT, _PT, _PT, c_void_p]
+_lib.fa_b200_bwd_noalloc.restype = c_int
 _lib.fa_b200_bwd_sm_clock.argtypes = [_PP, c_void_p, POINTER(ctypes.c_uint64), POINTER(ctypes.c_uint64)]
 _lib.fa_b200_bwd_sm_clock.restype = c_int
 _lib.fa_b200_merge.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]
@@ -157,6 +159,21 @@ def bwd(prob: Problem, q, k, v, o, dout, lse, dq, dk, dv, workspace) -> None:
                               workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                               _stream(q))
     _check(rc, "fa_b200_bwd")
+
+
+NOALLOC_SCRATCH_BYTES = 32 << 20  # FA_B200_NOALLOC_SCRATCH_BYTES of include/fa_b200.h
+
+
+def bwd_noalloc(prob: Problem, q, k, v, o, dout, lse, dq, dk, dv) -> None:
+    """fa_b200_bwd_noalloc: :func:`bwd` with the library's static device scratch as workspace (no
+    allocation inside the call; problems needing more than NOALLOC_SCRATCH_BYTES are refused; calls
+    that overlap on one GPU race on the shared scratch)."""
+    _require_cuda(q, k, v, o, dout, lse, dq, dk, dv)
+    with torch.cuda.device(q.device):
+        rc = _lib.fa_b200_bwd_noalloc(byref(prob), byref(_tensor(q)), byref(_tensor(k)), byref(_tensor(v)),
+                                      byref(_tensor(o)), byref(_tensor(dout)), lse.data_ptr(),
+                                      byref(_tensor(dq)), byref(_tensor(dk)), byref(_tensor(dv)), _stream(q))
+    _check(rc, "fa_b200_bwd_noalloc")
 
 
 def bwd_dq_accum(prob: Problem, q, k, v, o, dout, lse, dq_acc, dk, dv, workspace) -> None:

@@ -489,6 +489,32 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   return launched();
 }
 
+// ---------------------------------------------------------------- backward scratch that is never allocated
+// Workspace of fa_b200_bwd_noalloc: a file-scope device array (one copy on every GPU that loads this
+// library, held until the process exits) instead of memory the caller obtained from cudaMalloc.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[FA_B200_NOALLOC_SCRATCH_BYTES];
+
+void *noalloc_scratch_ptr(int *rc) {
+  static std::atomic<void *> base[64];
+  int dev = 0;
+  *rc = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { *rc = fail(FA_B200_ERR_CUDA, "cudaGetDevice failed"); return nullptr; }
+  const bool cached = dev >= 0 && dev < 64;
+  void *ptr = cached ? base[dev].load(std::memory_order_acquire) : nullptr;
+  if (!ptr) {
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+      *rc = fail(FA_B200_ERR_CUDA, "cudaGetSymbolAddress of the static backward scratch failed on device %d: %s", dev,
+                 cudaGetErrorString(e));
+      return nullptr;
+    }
+    if (cached) base[dev].store(ptr, std::memory_order_release);
+  }
+  return ptr;
+}
+
 }  // namespace
 
 // ================================================================== extern "C"
@@ -669,6 +695,25 @@ int fa_b200_merge_acc(float *o_acc, float *lse_acc, const void *o_b, const float
       return fail(FA_B200_ERR_UNSUPPORTED, "unknown dtype %d", dtype_b);
   }
   return launched();
+}
+
+int fa_b200_bwd_noalloc(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                        const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                        const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+                        const fa_b200_tensor *dv, void *stream) {
+  if (int rc = check_problem(p)) return rc;
+  const size_t need = fa_b200_bwd_workspace_bytes(p);
+  if (need > (size_t)FA_B200_NOALLOC_SCRATCH_BYTES)
+    return fail(FA_B200_ERR_WORKSPACE,
+                "fa_b200_bwd_noalloc: this problem needs %zu bytes of scratch, the static scratch holds %zu "
+                "(FA_B200_NOALLOC_SCRATCH_BYTES); use fa_b200_bwd with a caller-provided workspace",
+                need, (size_t)FA_B200_NOALLOC_SCRATCH_BYTES);
+  int rc = 0;
+  void *scratch = noalloc_scratch_ptr(&rc);
+  if (rc) return rc;
+  // everything in the scratch that must start at zero (dQ accumulator, work counter, dQ semaphores) is
+  // cleared by fa_bwd_prep_kernel on `stream` at the start of every backward; the rest is overwritten
+  return fa_b200_bwd(p, q, k, v, o, dout, lse, dq, dk, dv, scratch, (size_t)FA_B200_NOALLOC_SCRATCH_BYTES, stream);
 }
 
 }  // extern "C"

@@ -100,6 +100,23 @@ int fa_b200_bwd_dq_accum(const fa_b200_problem *p, const fa_b200_tensor *q, cons
                          const float *lse, const fa_b200_tensor *dq_acc, const fa_b200_tensor *dk,
                          const fa_b200_tensor *dv, void *workspace, size_t workspace_bytes, void *stream);
 
+/* Backward without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same computation and results as fa_b200_bwd, but the
+ * workspace is a static __device__ array inside the library, FA_B200_NOALLOC_SCRATCH_BYTES (32 MiB)
+ * on every GPU that loads the library, held until the process exits.  Problems with
+ * fa_b200_bwd_workspace_bytes(p) above that limit are refused with FA_B200_ERR_WORKSPACE (tensor
+ * path: about B*H*Lq*(4*D + 24) bytes, e.g. B*H = 8, Lq = 4096, D = 128 needs 17 MiB).  The call
+ * itself makes no cudaMalloc / cudaFree and uses no allocating library routine.  ALL calls on a
+ * device share the one array, which keeps the previous call's contents: what has to start at zero
+ * (dQ accumulator, work counter, semaphores) is cleared on `stream` at the start of every call, and
+ * calls that overlap on the GPU (two streams, or two host threads on one device) RACE -- order them. */
+#define FA_B200_NOALLOC_SCRATCH_BYTES (32u << 20)
+int fa_b200_bwd_noalloc(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_tensor *k,
+                        const fa_b200_tensor *v, const fa_b200_tensor *o, const fa_b200_tensor *dout,
+                        const float *lse, const fa_b200_tensor *dq, const fa_b200_tensor *dk,
+                        const fa_b200_tensor *dv, void *stream);
+
 /* Measurement hook (no reference counterpart; the reference's C++ benchmark reads
  * poplar::cycleCount the same way, tests/cpp/test_flash_attention.cpp:236-239): SM cycles and
  * nanoseconds that CTA 0 of the last tensor-family backward kernel launched with `workspace`
