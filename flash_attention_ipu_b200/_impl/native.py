@@ -5,7 +5,7 @@ device pointers + element strides; the stream is torch's current CUDA stream.  E
 as negative status codes and are raised as ``RuntimeError`` with ``fa_b200_last_error()``.
 """
 import ctypes
-from ctypes import POINTER, Structure, byref, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
+from ctypes import POINTER, Structure, byref, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint64, c_void_p
 
 import torch
 
@@ -32,7 +32,7 @@ class Problem(Structure):  # fa_b200_problem
         ("B", c_int32), ("H", c_int32), ("Lq", c_int32), ("Lk", c_int32), ("D", c_int32),
         ("dtype", c_int32), ("causal", c_int32), ("softmax_scale", c_float),
         ("block_q_hint", c_int32), ("block_kv_hint", c_int32), ("q_pos0", c_int32), ("kv_pos0", c_int32),
-        ("H_kv", c_int32), ("kv_lens", c_void_p),
+        ("H_kv", c_int32), ("kv_lens", c_void_p), ("dropout_p", c_float), ("dropout_seed", c_uint64),
     ]
 
 
@@ -114,7 +114,7 @@ def _require_cuda(*ts: torch.Tensor) -> None:
 
 def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
                  block_q: int = 0, block_kv: int = 0, q_pos0: int = 0, kv_pos0: int = 0,
-                 kv_lens: "torch.Tensor | None" = None) -> Problem:
+                 kv_lens: "torch.Tensor | None" = None, dropout_p: float = 0.0, dropout_seed: int = 0) -> Problem:
     if q.dtype not in _DTYPES:
         raise RuntimeError(f"unsupported dtype {q.dtype}")
     B, H, Lq, D = q.shape
@@ -127,7 +127,8 @@ def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
             raise RuntimeError("kv_lens must be a contiguous CUDA int32 tensor with B*H entries")
         lens_ptr = kv_lens.data_ptr()
     return Problem(B, H, Lq, k.shape[2], D, _DTYPES[q.dtype], int(bool(causal)), float(scale),
-                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv, lens_ptr)
+                   int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv, lens_ptr,
+                   float(dropout_p), int(dropout_seed) & 0xFFFFFFFFFFFFFFFF)
 
 
 def kernel_family(prob: Problem) -> int:

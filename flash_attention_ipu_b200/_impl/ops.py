@@ -9,7 +9,8 @@ Like the reference's, the ops are registered natively: ``csrc/torch_ops.cpp`` (b
 ``cpp/flash_attention_qkv_packed.cpp:618-625``).  This module loads it, adds the shape-only
 ("fake") implementations that tracing needs, and exposes the four ops under their names:
 
-    flash_attention_ipu::attention_fwd(q, k, v, softmax_scale, causal, block_q, block_kv, kv_lens=None) -> (out, lse)
+    flash_attention_ipu::attention_fwd(q, k, v, softmax_scale, causal, block_q, block_kv,
+                                       kv_lens=None, dropout_p=0.0, dropout_seed=0)       -> (out, lse)
     flash_attention_ipu::attention_bwd(dout, q, k, v, out, lse, ...)                      -> (dq, dk, dv)
     flash_attention_ipu::qkv_packed_fwd(qkv, softmax_scale, causal, block_q, block_kv)    -> (out, lse)
     flash_attention_ipu::qkv_packed_bwd(dout, qkv, out, lse, ...)                         -> dqkv
@@ -62,20 +63,20 @@ def _like_kernel_view(t):
 
 
 @torch.library.register_fake("flash_attention_ipu::attention_fwd")
-def _(q, k, v, softmax_scale, causal, block_q, block_kv, kv_lens=None):
+def _(q, k, v, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0):
     return _like_kernel_view(q), q.new_empty(q.shape[:3], dtype=torch.float32)
 
 
 @torch.library.register_fake("flash_attention_ipu::attention_bwd")
-def _(dout, q, k, v, out, lse, softmax_scale, causal, block_q, block_kv, kv_lens=None):
+def _(dout, q, k, v, out, lse, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0):
     return _like_kernel_view(q), _like_kernel_view(k), _like_kernel_view(v)
 
 
 @torch.library.register_fake("flash_attention_ipu::qkv_packed_fwd")
-def _(qkv, softmax_scale, causal, block_q, block_kv, kv_lens=None):
+def _(qkv, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0):
     return qkv.new_empty(qkv.shape[1:]), qkv.new_empty(qkv.shape[1:3], dtype=torch.float32)
 
 
 @torch.library.register_fake("flash_attention_ipu::qkv_packed_bwd")
-def _(dout, qkv, out, lse, softmax_scale, causal, block_q, block_kv, kv_lens=None):
+def _(dout, qkv, out, lse, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0):
     return torch.empty_like(qkv)

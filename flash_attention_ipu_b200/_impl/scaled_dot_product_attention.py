@@ -3,7 +3,7 @@ reference's ``_impl/scaled_dot_product_attention.py:11-61``.
 
 Kept: the patching mechanism (``patch_function``), the ``NotImplementedError`` gates for
 attn_mask / dropout / q,k,v shape mismatch (:21-41, applied before the device check exactly as
-in the reference), the chunk heuristic (:52-53, now only a tile hint) and the pass-through to the
+in the reference; one boolean key-padding mask form and dropout on the tensor path are taken), the chunk heuristic (:52-53, now only a tile hint) and the pass-through to the
 original function for tensors that are not on our device (:60-61).
 Changed (documented deviations): ``is_causal=False`` is routed to the
 kernel instead of raising (needed by BASELINE.json config 4); ``attn_mask is not None`` replaces
@@ -70,8 +70,17 @@ def _sdpa_impl(
             raise NotImplementedError(
                 "flash_attention_ipu supports attn_mask only as a boolean key-padding mask of shape "
                 "(B, 1, 1, Lk) whose True entries form a prefix of every row (bf16 / fp16, D in {64, 128})")
+    dropout_seed = 0
     if dropout_p > 0.0:
-        raise NotImplementedError("flash_attention_ipu does not currently support non-zero dropout_p")
+        # The reference refuses dropout (:25-28).  Here the tcgen05 kernels apply it (16-bit, D in {64, 128});
+        # everything else keeps the reference's error.  The seed comes from torch's CPU generator (no device
+        # synchronisation; repeatable under torch.manual_seed) and travels to the backward through autograd.
+        if not (query.ndim == 4 and query.is_cuda and query.dtype in (torch.bfloat16, torch.float16)
+                and query.shape[-1] in (64, 128) and dropout_p < 1.0):
+            raise NotImplementedError(
+                "flash_attention_ipu does not currently support non-zero dropout_p "
+                "(only for 4-D bf16 / fp16 CUDA tensors with D in {64, 128} and dropout_p < 1)")
+        dropout_seed = int(torch.randint(0, 2 ** 62, (1,)).item())
     gqa = (enable_gqa and query.ndim == 4 and key.ndim == 4 and key.shape == value.shape
            and query.shape[0] == key.shape[0] and query.shape[2:] == key.shape[2:]
            and key.shape[1] > 0 and query.shape[1] % key.shape[1] == 0
@@ -106,7 +115,7 @@ def _sdpa_impl(
     else:
         q, k, v = (t.reshape(1, -1, L, D) for t in (query, key, value))
     out, _lse = ops.attention_fwd(q, k, v, softmax_scale, bool(is_causal),
-                                  L // num_chunks_q, L // num_chunks_kv, kv_lens)
+                                  L // num_chunks_q, L // num_chunks_kv, kv_lens, float(dropout_p), dropout_seed)
     return out.reshape(*batch_shape, L, D) if query.ndim != 4 else out
 
 

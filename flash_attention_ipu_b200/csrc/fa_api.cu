@@ -62,6 +62,12 @@ int check_problem(const fa_b200_problem *p) {
     return fail(FA_B200_ERR_UNSUPPORTED, "head dim %d > %d", p->D, fa::kGenMaxD);
   if (p->kv_lens && !(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
     return fail(FA_B200_ERR_UNSUPPORTED, "kv_lens (key padding) needs the tensor path (16-bit, D in {64,128})");
+  if (!(p->dropout_p >= 0.f && p->dropout_p < 1.f)) return fail(FA_B200_ERR_INVALID, "dropout_p must be in [0, 1)");
+  if (p->dropout_p > 0.f) {
+    if (!(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
+      return fail(FA_B200_ERR_UNSUPPORTED, "dropout needs the tensor path (16-bit, D in {64,128})");
+    if (p->kv_pos0 % 4) return fail(FA_B200_ERR_INVALID, "dropout needs kv_pos0 to be a multiple of 4 (one hash word covers 4 keys)");
+  }
   // every kernel folds (tiles x groups) into a 1-D grid
   const int64_t lmax = p->Lq > p->Lk ? p->Lq : p->Lk;
   if ((int64_t)p->B * p->H * ((lmax + 63) / 64) > INT32_MAX)
@@ -78,6 +84,17 @@ int check_tensor(const fa_b200_tensor *t, const char *name) {
 bool tma_ok(const fa_b200_tensor *t, size_t es) {
   return (reinterpret_cast<uintptr_t>(t->ptr) % 16 == 0) && (t->stride_l * es) % 16 == 0 &&
          (t->stride_h * es) % 16 == 0 && (t->stride_b * es) % 16 == 0 && t->stride_l > 0;
+}
+
+// dropout: 8-bit threshold (drop probability thresh / 256), the survivors' scale and the 32-bit seed fold
+uint32_t drop_thresh(const fa_b200_problem *p) {
+  if (!(p->dropout_p > 0.f)) return 0;
+  long t = lroundf(p->dropout_p * 256.f);
+  return (uint32_t)(t < 1 ? 1 : t > 255 ? 255 : t);
+}
+float drop_scale(const fa_b200_problem *p) { return 256.f / (256.f - (float)drop_thresh(p)); }
+uint32_t drop_seed32(const fa_b200_problem *p) {
+  return (uint32_t)p->dropout_seed ^ ((uint32_t)(p->dropout_seed >> 32) * 0x9E3779B1u);
 }
 
 int family(const fa_b200_problem *p) {
@@ -336,10 +353,12 @@ int sm_count() {  // per device: a process may drive several GPUs
 }
 
 // Work counters of the persistent forward (the backward keeps its counter in its workspace; the
-// forward has none).  A ring of kFwdCounters 4-byte slots per device, allocated once; every launch
+// forward has none).  A ring of kFwdCounters 4-byte slots per device in a static device array (the
+// library allocates nothing; address looked up once per device with that device current); every launch
 // takes the next slot and zeroes it ON ITS STREAM right before the kernel, so launches on different
 // streams never share a counter unless kFwdCounters of them are in flight at once.
 constexpr int kFwdCounters = 1024;
+static __device__ __align__(256) int g_fwd_counters[kFwdCounters];  // host code: a symbol, not an address
 int *fwd_counter_slot(cudaStream_t st, int *rc) {
   static std::atomic<int *> base[64];
   static std::atomic<unsigned> next{0};
@@ -352,8 +371,8 @@ int *fwd_counter_slot(cudaStream_t st, int *rc) {
     std::lock_guard<std::mutex> lock(mu);
     b = base[dev & 63].load(std::memory_order_acquire);
     if (!b) {
-      if (cudaMalloc(&b, kFwdCounters * sizeof(int)) != cudaSuccess) {
-        *rc = fail(FA_B200_ERR_CUDA, "cudaMalloc of the forward work counters failed");
+      if (cudaGetSymbolAddress(reinterpret_cast<void **>(&b), g_fwd_counters) != cudaSuccess || !b) {
+        *rc = fail(FA_B200_ERR_CUDA, "cudaGetSymbolAddress of the forward work counters failed");
         return nullptr;
       }
       base[dev & 63].store(b, std::memory_order_release);
@@ -387,9 +406,15 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const int64_t items = (int64_t)p->B * p->H * fp.num_pairs;
   if (items > INT32_MAX) return fail(FA_B200_ERR_UNSUPPORTED, "too many Q tile pairs (%lld)", (long long)items);
   fp.num_items = (int)items;
-  auto kern = fa::fa_fwd_sm100_kernel<D, kBf16>;
-  static std::atomic<uint64_t> smem_ok{0};  // per instantiation
-  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok)) return rc;
+  const bool drop = drop_thresh(p) > 0;
+  fp.drop_thresh4 = drop_thresh(p) * 0x01010101u;
+  fp.drop_seed = drop_seed32(p);
+  fp.drop_scale = drop_scale(p);
+  fp.drop_q0 = p->q_pos0;
+  fp.drop_k40 = p->kv_pos0 / 4;
+  auto kern = drop ? fa::fa_fwd_sm100_kernel<D, kBf16, true> : fa::fa_fwd_sm100_kernel<D, kBf16, false>;
+  static std::atomic<uint64_t> smem_ok[2] = {{0}, {0}};  // per instantiation
+  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok[drop])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory); with no more items
   // than SMs every CTA runs exactly one and no counter is needed
   const int sms = sm_count();
@@ -458,10 +483,16 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const int64_t items = (int64_t)p->B * Hkv * bp.num_kv_tiles;  // one work item per (batch, K/V head, KV tile)
   if (items > INT32_MAX) return fail(FA_B200_ERR_UNSUPPORTED, "too many KV tiles (%lld)", (long long)items);
   bp.num_items = (int)items;
-  const bool gqa = bp.kv_ratio > 1;
-  auto kern = gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false>;
-  static std::atomic<uint64_t> smem_ok[2] = {{0}, {0}};
-  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa])) return rc;
+  const bool gqa = bp.kv_ratio > 1, drop = drop_thresh(p) > 0;
+  bp.drop_thresh4 = drop_thresh(p) * 0x01010101u;
+  bp.drop_seed = drop_seed32(p);
+  bp.drop_scale = drop_scale(p);
+  bp.drop_q0 = p->q_pos0;
+  bp.drop_k40 = p->kv_pos0 / 4;
+  auto kern = drop ? (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false, true>)
+                   : (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, false> : fa::fa_bwd_sm100_kernel<D, kBf16, false, false>);
+  static std::atomic<uint64_t> smem_ok[4] = {{0}, {0}, {0}, {0}};
+  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * drop])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory), items by atomic counter
   const unsigned grid = (unsigned)(items < sm_count() ? items : sm_count());
 #ifdef FA_BWD_TRACE

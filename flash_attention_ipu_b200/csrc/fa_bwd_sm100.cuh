@@ -69,6 +69,10 @@ struct BwdParams {
   float scale, scale_log2;
   int num_kv_tiles;    // ceil(Lk / 128)
   int num_items;       // B * Hkv * num_kv_tiles
+  // dropout (kDrop instantiation only), as in FwdParams: the same hash regenerates the forward's mask
+  uint32_t drop_thresh4, drop_seed;
+  float drop_scale;
+  int drop_q0, drop_k40;
 #ifdef FA_BWD_TRACE
   unsigned long long *trace;  // CTA 0: cycles the MMA warp spent in each of its waits
 #endif
@@ -142,7 +146,10 @@ __device__ __forceinline__ void bwd_next_tile(int &h, int &i, int i0, int num_q_
 // kGqa = several query heads share the CTA's K/V head (the Q-tile loop then walks head by head);
 // the multi-head instantiation keeps the plain induction variable, which the compiler holds in
 // uniform registers (the loop-carried (h, i) pair cost 6 % of the backward).
-template <int D, bool kBf16, bool kGqa>
+// kDrop = dropout on P: with M the keep mask and s = 1 / (1 - p), the forward computed O = s (M o P) V, so
+//   dV = s (M o P)^T dO   (the thinned P^T is the A operand; s is applied once, at the item's end)
+//   dS = P o (s M o dP - delta)   with delta = rowsum(O o dO) as before and P the UNdropped softmax.
+template <int D, bool kBf16, bool kGqa, bool kDrop = false>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -476,6 +483,25 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           const float4 l4 = stat[c4];
           nl[4 * c4] = l4.x; nl[4 * c4 + 1] = l4.y; nl[4 * c4 + 2] = l4.z; nl[4 * c4 + 3] = l4.w;
         }
+        // dropout: bit c of keepm = query column c of this warpgroup keeps this thread's key (generated
+        // ahead of the S^T wait; sm100_ptx.cuh: drop_hash -- thread <-> key, so one hash per query)
+        uint32_t keepm[2] = {0xffffffffu, 0xffffffffu};
+        if (kDrop) {
+          const uint32_t kh = drop_seed_of_group(p.drop_seed, static_cast<uint32_t>(t.b * p.H + t.h0 + hx)) ^
+                              (static_cast<uint32_t>(p.drop_k40 + (key >> 2)) * 0x85EBCA77u);
+          const uint32_t sh = (key & 3) * 8, th = p.drop_thresh4 & 0xffu;
+          const uint32_t q0 = static_cast<uint32_t>(p.drop_q0 + i * 128 + 64 * wg);
+          #pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            uint32_t m = 0;
+            #pragma unroll
+            for (int c = 0; c < 32; ++c) {
+              const uint32_t byte = (drop_mix(kh ^ ((q0 + hf * 32 + c) * 0x9E3779B1u)) >> sh) & 0xffu;
+              m |= (byte >= th ? 1u : 0u) << c;
+            }
+            keepm[hf] = m;
+          }
+        }
         mbar_wait(s_full, git & 1);
         tc_fence_after();
         float pr[64];
@@ -523,7 +549,13 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         {
           uint32_t pk[32];
           #pragma unroll
-          for (int c = 0; c < 32; ++c) pk[c] = pack2<kBf16>(pr[2 * c], pr[2 * c + 1]);
+          for (int c = 0; c < 32; ++c) {
+            pk[c] = pack2<kBf16>(pr[2 * c], pr[2 * c + 1]);
+            if (kDrop) {  // thin the dV operand only; pr stays the undropped softmax for dS
+              const uint32_t two = (keepm[c >> 4] >> ((2 * c) & 31)) & 3u;
+              pk[c] &= ((two & 1u) ? 0x0000ffffu : 0u) | ((two & 2u) ? 0xffff0000u : 0u);
+            }
+          }
           tmem_st32(tS, pk);  // P^T over the first half of this warpgroup's own S^T columns
           tmem_st_wait();
           tc_fence_before();
@@ -548,6 +580,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           #pragma unroll
           for (int c = 0; c < 32; c += 2) {
             float a0, a1;
+            if (kDrop) {
+              const uint32_t d0 = (keepm[hf] >> c) & 1u ? dp[c] : 0u, d1 = (keepm[hf] >> (c + 1)) & 1u ? dp[c + 1] : 0u;
+              f2_unpack(f2_mul(f2_pack(pr[hf * 32 + c], pr[hf * 32 + c + 1]),
+                               f2_fma(f2_pack(d0, d1), f2_pack(p.drop_scale, p.drop_scale), f2_pack(nd[c], nd[c + 1]))), a0, a1);
+            } else
             f2_unpack(f2_mul(f2_pack(pr[hf * 32 + c], pr[hf * 32 + c + 1]),
                              f2_add(f2_pack(dp[c], dp[c + 1]), f2_pack(nd[c], nd[c + 1]))), a0, a1);
             wd[c >> 1] = pack2<kBf16>(a0, a1);
@@ -590,7 +627,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const int which = (D == 128) ? round : wg;  // 0 = dK, 1 = dV
         const int half = (D == 128) ? wg : 0;       // which 64-column slab of the tile
         const uint32_t tsrc = tmem_base + (which == 0 ? kColDK : kColDV) + lane_addr + 64 * half;
-        const float mul = which == 0 ? p.scale : 1.f;
+        const float mul = which == 0 ? p.scale : (kDrop ? p.drop_scale : 1.f);
         uint8_t *dst_row = smem + L::kDSOff + wg * L::kHalfBytes + row * 128;
         #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {

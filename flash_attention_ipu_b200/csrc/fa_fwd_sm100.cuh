@@ -77,6 +77,11 @@ struct FwdParams {
   float scale_log2;   // softmax_scale * log2(e)
   int num_pairs;      // ceil(Lq / 256)
   int num_items;      // B * H * num_pairs
+  // dropout on P (kDrop instantiation only; sm100_ptx.cuh: drop_hash): keep key iff its hash byte >= thresh
+  uint32_t drop_thresh4;  // thresh * 0x01010101
+  uint32_t drop_seed;     // 32-bit fold of fa_b200_problem.dropout_seed
+  float drop_scale;       // 256 / (256 - thresh)
+  int drop_q0, drop_k40;  // q_pos0 ; kv_pos0 / 4 (global positions feed the hash)
 };
 
 template <int D>
@@ -124,7 +129,7 @@ __device__ __forceinline__ FwdItem fwd_decode(const FwdParams &p, int w) {
   return t;
 }
 
-template <int D, bool kBf16>
+template <int D, bool kBf16, bool kDrop = false>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -327,6 +332,9 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const FwdItem t = fwd_decode(p, w);
       const int row = (t.t0 + i) * kBlockM + row_in_tile;
       const int n = i ? t.n1 : t.n0;
+      // dropout: the query's half of the hash input (sm100_ptx.cuh: drop_hash)
+      const uint32_t drop_qh = kDrop ? drop_seed_of_group(p.drop_seed, static_cast<uint32_t>(t.g)) ^
+                                       (static_cast<uint32_t>(p.drop_q0 + row) * 0x9E3779B1u) : 0u;
 
       float m_used = -INFINITY;  // reference max (log2 domain) the exponentials are taken against
       float l = 0.f;
@@ -387,6 +395,13 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           #pragma unroll
           for (int c = 0; c < 4; ++c) {
             uint32_t pk[16];
+            uint32_t keep[8];  // dropout: per-byte keep masks of this chunk's 8 groups of 4 keys
+            if (kDrop) {
+              const uint32_t k4 = static_cast<uint32_t>(p.drop_k40 + (col0 >> 2) + c * 8);
+              #pragma unroll
+              for (int g4 = 0; g4 < 8; ++g4)
+                keep[g4] = drop_keep_bytes(drop_mix(drop_qh ^ ((k4 + g4) * 0x85EBCA77u)), p.drop_thresh4);
+            }
             #pragma unroll
             for (int e = 0; e < 32; e += 2) {
               float x0, x1, p0, p1;
@@ -400,6 +415,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
               }
               sum2[(e >> 1) & 3] = f2_add(sum2[(e >> 1) & 3], f2_pack(p0, p1));
               pk[e >> 1] = pack2<kBf16>(p0, p1);
+              // the row sum above is of the UNdropped P (softmax denominator); only the PV operand is thinned
+              if (kDrop) pk[e >> 1] &= __byte_perm(keep[e >> 2], 0u, ((e >> 1) & 1) ? 0x3322u : 0x1100u);
             }
             tmem_st16(tS + c * 16, pk);
             if ((c + 1) % (4 / kPSplit) == 0) {  // this group of P columns is complete: release it
@@ -420,7 +437,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       // ---------------- item end: O_i / l -> global (straight from registers) ; LSE ----------------
       // Each thread owns one output row (D contiguous 16-bit values): 16-byte stores, two per 32-byte
       // sector.  No shared-memory staging: the Q buffers already belong to the next item.
-      const float inv_l = l > 0.f ? 1.f / l : 0.f;
+      const float inv_l = (l > 0.f ? 1.f / l : 0.f) * (kDrop ? p.drop_scale : 1.f);
       if (n > 0) {
         mbar_wait(&o_full[i], co & 1);
         tc_fence_after();

@@ -530,4 +530,25 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   return r;
 }
 
+// ---------------------------------------------------------------- dropout (counter-based, no state)
+// One 32-bit hash decides FOUR neighbouring keys of one query: byte b of drop_hash(seed_g, q, k >> 2)
+// belongs to key k (b = k & 3), and the key is KEPT iff that byte >= thresh (thresh = round(256 p),
+// so the drop probability is thresh / 256 and the survivors are scaled by 256 / (256 - thresh)).
+// q, k are GLOBAL sequence positions (q_pos0 + row, kv_pos0 + key), so the forward, the backward
+// and every ring hop regenerate the same mask.  The mixer is the public-domain "lowbias32"
+// integer finaliser.  Restated on the CPU by oracle/attention_oracle.py:dropout_keep_mask.
+__host__ __device__ __forceinline__ uint32_t drop_mix(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+__host__ __device__ __forceinline__ uint32_t drop_hash(uint32_t seed_g, uint32_t q, uint32_t k4) {
+  return drop_mix(seed_g ^ (q * 0x9E3779B1u) ^ (k4 * 0x85EBCA77u));
+}
+// per (batch, query head) stream: g = b * H + h
+__host__ __device__ __forceinline__ uint32_t drop_seed_of_group(uint32_t seed, uint32_t g) {
+  return drop_mix(seed ^ (g * 0xC2B2AE3Du + 0x27D4EB2Fu));
+}
+// per-byte "keep" mask (0xff / 0x00) of the four keys of one hash word; thresh4 = thresh * 0x01010101
+__device__ __forceinline__ uint32_t drop_keep_bytes(uint32_t hash, uint32_t thresh4) { return __vcmpgeu4(hash, thresh4); }
+
 }  // namespace fa

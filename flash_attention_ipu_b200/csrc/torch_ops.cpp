@@ -101,7 +101,8 @@ Tensor lens_or_empty(const std::optional<Tensor> &kv_lens, const Tensor &q) {
 }
 
 fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, double scale, int64_t block_q,
-                             int64_t block_kv, const Tensor &lens = Tensor()) {
+                             int64_t block_kv, const Tensor &lens = Tensor(), double dropout_p = 0.0,
+                             int64_t dropout_seed = 0) {
   TORCH_CHECK(q.dim() == 4 && k.dim() == 4, "expected (B, H, L, D) operands");
   const int64_t H = q.size(1), Hkv = k.size(1);
   TORCH_CHECK(Hkv > 0 && H % Hkv == 0, H, " query heads are not a multiple of ", Hkv, " key/value heads");
@@ -120,6 +121,8 @@ fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, doub
   p.kv_pos0 = 0;
   p.H_kv = Hkv == H ? 0 : static_cast<int32_t>(Hkv);
   p.kv_lens = lens.defined() ? lens.data_ptr<int32_t>() : nullptr;
+  p.dropout_p = static_cast<float>(dropout_p);
+  p.dropout_seed = static_cast<uint64_t>(dropout_seed);
   return p;
 }
 
@@ -155,7 +158,7 @@ void run_bwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const T
 // ------------------------------------------------------------------ separate q, k, v (SDPA path)
 std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, const Tensor &v_, double scale,
                                          bool causal, int64_t block_q, int64_t block_kv,
-                                         const std::optional<Tensor> &kv_lens) {
+                                         const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed) {
   require_cuda({&q_, &k_, &v_});
   check_operands(q_, k_, v_, nullptr, nullptr, nullptr);
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_);
@@ -163,28 +166,30 @@ std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, con
   if (out.stride(-1) != 1) out = at::empty(q.sizes(), q.options());
   const Tensor lse = at::empty({q.size(0), q.size(1), q.size(2)}, q.options().dtype(at::kFloat));
   const Tensor lens = lens_or_empty(kv_lens, q);
-  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out, lse);
+  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed), q, k, v, out, lse);
   return {out, lse};
 }
 
 std::tuple<Tensor, Tensor, Tensor> attention_bwd(const Tensor &dout_, const Tensor &q_, const Tensor &k_,
                                                  const Tensor &v_, const Tensor &out_, const Tensor &lse_,
                                                  double scale, bool causal, int64_t block_q, int64_t block_kv,
-                                                 const std::optional<Tensor> &kv_lens) {
+                                                 const std::optional<Tensor> &kv_lens, double dropout_p,
+                                                 int64_t dropout_seed) {
   require_cuda({&dout_, &q_, &k_, &v_, &out_, &lse_});
   check_operands(q_, k_, v_, &out_, &dout_, &lse_);
   const Tensor lse = lse_.contiguous();  // the kernels index it as a dense [B*H][Lq] array
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_), out = as_bhld(out_), dout = as_bhld(dout_);
   const Tensor dq = at::empty_like(q), dk = at::empty_like(k), dv = at::empty_like(v);
   const Tensor lens = lens_or_empty(kv_lens, q);
-  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out, dout, lse, dq, dk, dv);
+  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed), q, k, v, out, dout, lse, dq, dk, dv);
   return {dq, dk, dv};
 }
 
 // ------------------------------------------------------------------ packed qkv (reference API)
 // (3,G,L,D) is B=1, H=G with q/k/v = base + {0,1,2}*G*L*D: zero-copy views.
 std::tuple<Tensor, Tensor> qkv_packed_fwd(const Tensor &qkv_, double scale, bool causal, int64_t block_q,
-                                          int64_t block_kv, const std::optional<Tensor> &kv_lens) {
+                                          int64_t block_kv, const std::optional<Tensor> &kv_lens, double dropout_p,
+                                          int64_t dropout_seed) {
   require_cuda({&qkv_});
   TORCH_CHECK(qkv_.dim() == 4 && qkv_.size(0) == 3, "expected a packed (3, G, L, D) tensor");
   const Tensor qkv = qkv_.contiguous();
@@ -192,13 +197,13 @@ std::tuple<Tensor, Tensor> qkv_packed_fwd(const Tensor &qkv_, double scale, bool
   const Tensor out = at::empty({qkv.size(1), qkv.size(2), qkv.size(3)}, qkv.options());
   const Tensor lse = at::empty({qkv.size(1), qkv.size(2)}, qkv.options().dtype(at::kFloat));
   const Tensor lens = lens_or_empty(kv_lens, q);
-  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out.unsqueeze(0), lse);
+  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed), q, k, v, out.unsqueeze(0), lse);
   return {out, lse};
 }
 
 Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out_, const Tensor &lse_,
                       double scale, bool causal, int64_t block_q, int64_t block_kv,
-                      const std::optional<Tensor> &kv_lens) {
+                      const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed) {
   require_cuda({&dout_, &qkv_, &out_, &lse_});
   TORCH_CHECK(qkv_.dim() == 4 && qkv_.size(0) == 3, "expected a packed (3, G, L, D) tensor");
   TORCH_CHECK(dout_.dim() == 3 && out_.dim() == 3 && dout_.sizes() == out_.sizes() && out_.size(0) == qkv_.size(1) &&
@@ -211,7 +216,7 @@ Tensor qkv_packed_bwd(const Tensor &dout_, const Tensor &qkv_, const Tensor &out
   const Tensor q = qkv[0].unsqueeze(0), k = qkv[1].unsqueeze(0), v = qkv[2].unsqueeze(0);
   const Tensor dqkv = at::empty_like(qkv);  // gradients land directly in the packed buffer
   const Tensor lens = lens_or_empty(kv_lens, q);
-  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens), q, k, v, out.unsqueeze(0), dout.unsqueeze(0), lse,
+  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed), q, k, v, out.unsqueeze(0), dout.unsqueeze(0), lse,
           dqkv[0].unsqueeze(0), dqkv[1].unsqueeze(0), dqkv[2].unsqueeze(0));
   return dqkv;
 }
@@ -228,12 +233,14 @@ auto typed_op(const char *name) {
 struct AttentionFn : public torch::autograd::Function<AttentionFn> {
   static variable_list forward(AutogradContext *ctx, const Tensor &q, const Tensor &k, const Tensor &v,
                                double scale, bool causal, int64_t block_q, int64_t block_kv,
-                               const std::optional<Tensor> &kv_lens) {
+                               const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed) {
     at::AutoDispatchBelowADInplaceOrView below;
     static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, const Tensor &, const Tensor &, double,
-                                                         bool, int64_t, int64_t, const std::optional<Tensor> &)>(
-        "flash_attention_ipu::attention_fwd");
-    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv, kv_lens);
+                                                         bool, int64_t, int64_t, const std::optional<Tensor> &, double,
+                                                         int64_t)>("flash_attention_ipu::attention_fwd");
+    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed);
+    ctx->saved_data["dropout_p"] = dropout_p;      // the backward regenerates the forward's mask from the seed
+    ctx->saved_data["dropout_seed"] = dropout_seed;
     ctx->save_for_backward({q, k, v, out, lse, kv_lens.has_value() ? *kv_lens : Tensor()});
     ctx->saved_data["scale"] = scale;
     ctx->saved_data["causal"] = causal;
@@ -245,25 +252,29 @@ struct AttentionFn : public torch::autograd::Function<AttentionFn> {
   static variable_list backward(AutogradContext *ctx, variable_list grads) {
     static auto op = typed_op<std::tuple<Tensor, Tensor, Tensor>(
         const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
-        int64_t, int64_t, const std::optional<Tensor> &)>("flash_attention_ipu::attention_bwd");
+        int64_t, int64_t, const std::optional<Tensor> &, double, int64_t)>("flash_attention_ipu::attention_bwd");
     const auto saved = ctx->get_saved_variables();
     const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[3]);
     const std::optional<Tensor> lens = saved[5].defined() ? std::optional<Tensor>(saved[5]) : std::nullopt;
     auto [dq, dk, dv] = op.call(dout, saved[0], saved[1], saved[2], saved[3], saved[4],
                                 ctx->saved_data["scale"].toDouble(), ctx->saved_data["causal"].toBool(),
-                                ctx->saved_data["block_q"].toInt(), ctx->saved_data["block_kv"].toInt(), lens);
-    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
+                                ctx->saved_data["block_q"].toInt(), ctx->saved_data["block_kv"].toInt(), lens,
+                                ctx->saved_data["dropout_p"].toDouble(), ctx->saved_data["dropout_seed"].toInt());
+    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
   }
 };
 
 struct PackedFn : public torch::autograd::Function<PackedFn> {
   static variable_list forward(AutogradContext *ctx, const Tensor &qkv, double scale, bool causal,
-                               int64_t block_q, int64_t block_kv, const std::optional<Tensor> &kv_lens) {
+                               int64_t block_q, int64_t block_kv, const std::optional<Tensor> &kv_lens,
+                               double dropout_p, int64_t dropout_seed) {
     at::AutoDispatchBelowADInplaceOrView below;
     static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, double, bool, int64_t, int64_t,
-                                                         const std::optional<Tensor> &)>(
+                                                         const std::optional<Tensor> &, double, int64_t)>(
         "flash_attention_ipu::qkv_packed_fwd");
-    auto [out, lse] = op.call(qkv, scale, causal, block_q, block_kv, kv_lens);
+    auto [out, lse] = op.call(qkv, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed);
+    ctx->saved_data["dropout_p"] = dropout_p;
+    ctx->saved_data["dropout_seed"] = dropout_seed;
     ctx->save_for_backward({qkv, out, lse, kv_lens.has_value() ? *kv_lens : Tensor()});
     ctx->saved_data["scale"] = scale;
     ctx->saved_data["causal"] = causal;
@@ -274,28 +285,31 @@ struct PackedFn : public torch::autograd::Function<PackedFn> {
   }
   static variable_list backward(AutogradContext *ctx, variable_list grads) {
     static auto op = typed_op<Tensor(const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
-                                     int64_t, int64_t, const std::optional<Tensor> &)>(
+                                     int64_t, int64_t, const std::optional<Tensor> &, double, int64_t)>(
         "flash_attention_ipu::qkv_packed_bwd");
     const auto saved = ctx->get_saved_variables();
     const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[1]);
     const std::optional<Tensor> lens = saved[3].defined() ? std::optional<Tensor>(saved[3]) : std::nullopt;
     const Tensor dqkv = op.call(dout, saved[0], saved[1], saved[2], ctx->saved_data["scale"].toDouble(),
                                 ctx->saved_data["causal"].toBool(), ctx->saved_data["block_q"].toInt(),
-                                ctx->saved_data["block_kv"].toInt(), lens);
-    return {dqkv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
+                                ctx->saved_data["block_kv"].toInt(), lens, ctx->saved_data["dropout_p"].toDouble(),
+                                ctx->saved_data["dropout_seed"].toInt());
+    return {dqkv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
   }
 };
 
 std::tuple<Tensor, Tensor> attention_fwd_autograd(const Tensor &q, const Tensor &k, const Tensor &v, double scale,
                                                   bool causal, int64_t block_q, int64_t block_kv,
-                                                  const std::optional<Tensor> &kv_lens) {
-  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv, kv_lens);
+                                                  const std::optional<Tensor> &kv_lens, double dropout_p,
+                                                  int64_t dropout_seed) {
+  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed);
   return {r[0], r[1]};
 }
 
 std::tuple<Tensor, Tensor> qkv_packed_fwd_autograd(const Tensor &qkv, double scale, bool causal, int64_t block_q,
-                                                   int64_t block_kv, const std::optional<Tensor> &kv_lens) {
-  auto r = PackedFn::apply(qkv, scale, causal, block_q, block_kv, kv_lens);
+                                                   int64_t block_kv, const std::optional<Tensor> &kv_lens,
+                                                   double dropout_p, int64_t dropout_seed) {
+  auto r = PackedFn::apply(qkv, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed);
   return {r[0], r[1]};
 }
 
@@ -304,14 +318,17 @@ std::tuple<Tensor, Tensor> qkv_packed_fwd_autograd(const Tensor &qkv, double sca
 TORCH_LIBRARY(flash_attention_ipu, m) {
   // kv_lens (optional, int32, one entry per (batch, head) group): key padding -- only the first kv_lens[g]
   // keys of group g exist.  The reference refuses every attn_mask (_impl/scaled_dot_product_attention.py:21-24).
+  // dropout_p / dropout_seed: dropout on the attention probabilities inside the tcgen05 kernels (the reference
+  // refuses dropout_p > 0, :25-28); the mask is a function of the seed, so the backward op takes the same pair.
   m.def("attention_fwd(Tensor q, Tensor k, Tensor v, float softmax_scale, bool causal, int block_q, "
-        "int block_kv, Tensor? kv_lens=None) -> (Tensor, Tensor)");
+        "int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> (Tensor, Tensor)");
   m.def("attention_bwd(Tensor dout, Tensor q, Tensor k, Tensor v, Tensor out, Tensor lse, float softmax_scale, "
-        "bool causal, int block_q, int block_kv, Tensor? kv_lens=None) -> (Tensor, Tensor, Tensor)");
+        "bool causal, int block_q, int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> "
+        "(Tensor, Tensor, Tensor)");
   m.def("qkv_packed_fwd(Tensor qkv, float softmax_scale, bool causal, int block_q, int block_kv, "
-        "Tensor? kv_lens=None) -> (Tensor, Tensor)");
+        "Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> (Tensor, Tensor)");
   m.def("qkv_packed_bwd(Tensor dout, Tensor qkv, Tensor out, Tensor lse, float softmax_scale, bool causal, "
-        "int block_q, int block_kv, Tensor? kv_lens=None) -> Tensor");
+        "int block_q, int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> Tensor");
 }
 
 // The implementations refuse non-CUDA tensors themselves ("there is no CPU path"), so they are

@@ -65,6 +65,13 @@ typedef struct {
                          /* attn_mask, which the reference refuses: _impl/scaled_dot_product_        */
                          /* attention.py:21-24).  All heads of a batch element must agree.  KV tiles  */
                          /* made of padding are skipped; dK = dV = 0 there.  Tensor path only.        */
+  float dropout_p;       /* dropout on the attention probabilities (the reference refuses dropout_p > 0: */
+                         /* _impl/scaled_dot_product_attention.py:25-28): 0 = none; else each (query,    */
+                         /* key) pair is dropped with probability round(256 p) / 256 and the survivors   */
+                         /* are scaled by its complement's inverse.  Tensor path only; kv_pos0 % 4 == 0. */
+  uint64_t dropout_seed; /* the mask is a pure function of (dropout_seed, b*H+h, q_pos0 + row,           */
+                         /* kv_pos0 + key) -- csrc/sm100_ptx.cuh: drop_hash -- so the backward must be   */
+                         /* given the forward's seed; restated by oracle/attention_oracle.py.            */
 } fa_b200_problem;
 
 /* Forward: replaces flashAttentionQKVPackedWithStash

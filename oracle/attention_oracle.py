@@ -170,3 +170,39 @@ def attention_flops(G: int, L: int, D: int, causal: bool, fwd: bool = True, bwd:
     """Algorithmic FLOPs: fwd 4*G*L^2*D, bwd 2.5x, halved if causal."""
     f = 4.0 * G * L * L * D * (0.5 if causal else 1.0)
     return f * ((1.0 if fwd else 0.0) + (2.5 if bwd else 0.0))
+
+
+_M32 = 0xFFFFFFFF
+
+
+def _drop_mix(x):
+    """lowbias32 integer finaliser on uint64 numpy arrays holding 32-bit values
+    (csrc/sm100_ptx.cuh: drop_mix)."""
+    x = x ^ (x >> 16)
+    x = (x * 0x7FEB352D) & _M32
+    x = x ^ (x >> 15)
+    x = (x * 0x846CA68B) & _M32
+    return x ^ (x >> 16)
+
+
+def dropout_keep_mask(seed: int, G: int, Lq: int, Lk: int, dropout_p: float, q_pos0: int = 0, kv_pos0: int = 0):
+    """The kernels' dropout mask, restated (no reference counterpart: the reference refuses
+    dropout_p > 0, _impl/scaled_dot_product_attention.py:25-28).  Returns (keep [G, Lq, Lk] bool
+    tensor, scale): key k of query q in group g is kept iff byte (k & 3) of
+    drop_hash(seed_g, q, k >> 2) >= round(256 p); survivors are scaled by 256 / (256 - round(256 p)).
+    Follows csrc/sm100_ptx.cuh (drop_hash, drop_seed_of_group) and csrc/fa_api.cu (drop_thresh,
+    drop_seed32); q, k are global positions (q_pos0 + row, kv_pos0 + key)."""
+    import numpy as np
+    p32 = float(np.float32(dropout_p))  # the C ABI carries dropout_p as a float
+    thresh = min(255, max(1, int(math.floor(p32 * 256.0 + 0.5)))) if p32 > 0 else 0
+    seed &= 0xFFFFFFFFFFFFFFFF
+    seed32 = (seed & _M32) ^ (((seed >> 32) * 0x9E3779B1) & _M32)
+    g = np.arange(G, dtype=np.uint64)
+    seed_g = _drop_mix(np.uint64(seed32) ^ ((g * 0xC2B2AE3D + 0x27D4EB2F) & _M32))      # [G]
+    q = ((np.arange(Lq, dtype=np.uint64) + np.uint64(q_pos0)) * 0x9E3779B1) & _M32        # [Lq]
+    kpos = np.arange(Lk, dtype=np.uint64) + np.uint64(kv_pos0)
+    k4 = ((kpos >> 2) * 0x85EBCA77) & _M32                                                # [Lk]
+    h = _drop_mix(seed_g[:, None, None] ^ q[None, :, None] ^ k4[None, None, :])
+    byte = (h >> ((kpos & 3) * 8)[None, None, :]) & 0xFF
+    keep = torch.from_numpy(byte >= thresh)
+    return keep, 256.0 / (256.0 - thresh)

@@ -750,3 +750,127 @@ def test_kv_lens_packed_api_and_skipped_tiles():
         assert rel_fro(x.grad[0, n].float(), q1.grad[0, 0].float()) < 1e-5
         assert torch.equal(x.grad[1, n, :m], k1.grad[0, 0, :m]) and torch.equal(x.grad[2, n, :m], v1.grad[0, 0, :m])
         assert torch.count_nonzero(x.grad[1:, n, m:]) == 0
+
+
+def _dropout_reference(q, k, v, dout, keep, drop_scale, causal, shift, scale):
+    """fp64 attention with dropout on the probabilities: out = drop_scale * (keep o softmax(S)) V; the
+    LSE is that of the undropped scores.  `keep` is (B, H, Lq, Lk) bool; k, v may have fewer heads."""
+    q, k, v = (t.double().requires_grad_(True) for t in (q, k, v))
+    rep = q.shape[1] // k.shape[1]
+    kk, vv = k.repeat_interleave(rep, dim=1), v.repeat_interleave(rep, dim=1)
+    s = torch.einsum("bhqd,bhkd->bhqk", q, kk) * scale
+    if causal:
+        r = torch.arange(q.shape[2])[:, None]
+        c = torch.arange(k.shape[2])[None, :]
+        s = s.masked_fill(c > r + shift, float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)
+    p = torch.where(torch.isinf(lse)[..., None], torch.zeros_like(s), torch.exp(s - lse[..., None].clamp_min(-1e300)))
+    out = torch.einsum("bhqk,bhkd->bhqd", p * keep.double() * drop_scale, vv)
+    out.backward(dout.double())
+    return out.detach(), lse.detach(), q.grad, k.grad, v.grad
+
+
+@pytest.mark.parametrize("B,H,Hkv,Lq,Lk,D,causal,q0,k0,dtype,p_drop", [
+    (1, 3, 3, 200, 328, 128, True, 128, 0, "bf16", 0.25),   # ragged, shifted diagonal (a ring hop's positions)
+    (2, 2, 2, 384, 384, 64, False, 0, 0, "fp16", 0.1),
+    (1, 4, 2, 256, 256, 128, True, 0, 64, "bf16", 0.5),     # grouped-query, key block ahead of the queries
+])
+def test_dropout_matches_the_hash_oracle(B, H, Hkv, Lq, Lk, D, causal, q0, k0, dtype, p_drop):
+    """fa_b200_problem.dropout_p / dropout_seed through the C ABI: the kernels' mask is the one
+    oracle/attention_oracle.py:dropout_keep_mask restates (forward AND backward regenerate it), the LSE
+    is that of the undropped scores, and out / dq / dk / dv match fp64 attention with that mask."""
+    native = _native_loaded()
+    torch.manual_seed(SEED + Lq + D)
+    dt = DT[dtype]
+    seed = 0x1234_5678_9ABC_DEF1
+    q, dout = (torch.randn(B, H, Lq, D).to(dt) for _ in range(2))
+    k, v = (torch.randn(B, Hkv, Lk, D).to(dt) for _ in range(2))
+    scale = D ** -0.5
+    keep, drop_scale = ao.dropout_keep_mask(seed, B * H, Lq, Lk, p_drop, q0, k0)
+    keep = keep.view(B, H, Lq, Lk)
+    assert abs(keep.float().mean().item() - (1 - p_drop)) < 0.02
+    ref = _dropout_reference(q.float(), k.float(), v.float(), dout.float(), keep, drop_scale, causal, q0 - k0, scale)
+    qd, kd, vd, dd = (t.cuda() for t in (q, k, v, dout))
+    prob = native.make_problem(qd, kd, causal, scale, 0, 0, q0, k0, dropout_p=p_drop, dropout_seed=seed)
+    assert native.kernel_family(prob) == 1
+    o = torch.empty_like(qd)
+    lse = torch.empty(B, H, Lq, device="cuda", dtype=torch.float32)
+    native.fwd(prob, qd, kd, vd, o, lse)
+    dq, dk, dv = torch.empty_like(qd), torch.empty_like(kd), torch.empty_like(vd)
+    ws = torch.empty(native.bwd_workspace_bytes(prob), device="cuda", dtype=torch.uint8)
+    native.bwd(prob, qd, kd, vd, o, dd, lse, dq, dk, dv, ws)
+    torch.cuda.synchronize()
+    finite = torch.isfinite(ref[1])
+    assert torch.equal(torch.isfinite(lse.cpu()), finite)
+    assert (lse.cpu().double()[finite] - ref[1][finite]).abs().max().item() <= 1e-2
+    # a wrong mask bit moves an output element by O(1); the 16-bit rounding of P moves it by ~1e-2
+    assert (o.cpu().double() - ref[0]).abs().max().item() <= 3e-2
+    assert rel_fro(o.cpu().double(), ref[0]) < 1e-2
+    for got, want in zip((dq, dk, dv), (ref[2], ref[3], ref[4])):
+        assert rel_fro(got.cpu().double(), want) < 1e-2
+    # the seed matters, and dropout_p = 0 is the plain kernel
+    prob2 = native.make_problem(qd, kd, causal, scale, 0, 0, q0, k0, dropout_p=p_drop, dropout_seed=seed + 1)
+    o2 = torch.empty_like(qd)
+    native.fwd(prob2, qd, kd, vd, o2, lse)
+    torch.cuda.synchronize()
+    assert not torch.equal(o2, o)
+    # refused off the tensor path
+    qf = torch.randn(1, 1, 64, 40, device="cuda")
+    with pytest.raises(RuntimeError, match="dropout"):
+        native.fwd(native.make_problem(qf, qf, True, 1.0, dropout_p=0.1), qf, qf, qf, torch.empty_like(qf),
+                   torch.empty(1, 1, 64, device="cuda"))
+
+
+def test_dropout_through_sdpa_override_and_packed_api():
+    """dropout_p > 0 through the public entry points: F.scaled_dot_product_attention (grouped-query, seed
+    drawn from torch's CPU generator, hence repeatable under torch.manual_seed) and
+    flash_attention_qkv_packed(dropout_p=, dropout_seed=); autograd carries the seed to the backward."""
+    import torch.nn.functional as F
+    import flash_attention_ipu as fa
+    import flash_attention_ipu_b200._impl.scaled_dot_product_attention as mod
+    native = _native_loaded()
+    torch.manual_seed(SEED)
+    B, H, Hkv, L, D, p_drop = 2, 4, 2, 256, 64, 0.2
+    q, dout = (torch.randn(B, H, L, D).bfloat16() for _ in range(2))
+    k, v = (torch.randn(B, Hkv, L, D).bfloat16() for _ in range(2))
+    mod.install()
+    try:
+        def run(seed_for_torch):
+            torch.manual_seed(seed_for_torch)
+            xs = [t.cuda().requires_grad_(True) for t in (q, k, v)]
+            before = native.launch_count()
+            out = F.scaled_dot_product_attention(*xs, dropout_p=p_drop, is_causal=True, enable_gqa=True)
+            out.backward(dout.cuda())
+            torch.cuda.synchronize()
+            assert native.launch_count() - before >= 3  # forward, prep, backward (+ convert): our kernels, not torch's
+            return [out.detach().cpu()] + [x.grad.cpu() for x in xs]
+        a, b, c = run(11), run(11), run(12)
+        assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])  # same seed, same mask
+        assert not torch.equal(a[0], c[0])
+        torch.manual_seed(11)
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())  # what the override drew
+    finally:
+        mod.uninstall()
+    keep, drop_scale = ao.dropout_keep_mask(seed, B * H, L, L, p_drop)
+    ref = _dropout_reference(q.float(), k.float(), v.float(), dout.float(), keep.view(B, H, L, L), drop_scale, True, 0, D ** -0.5)
+    assert rel_fro(a[0].double(), ref[0]) < 1e-2
+    for got, want in zip(a[1:], ref[2:]):
+        assert rel_fro(got.double(), want) < 1e-2
+
+    # packed API, explicit seed
+    G, L, D = 3, 256, 128
+    qkv = torch.randn(3, G, L, D)
+    qkv[0] *= D ** -0.5  # the packed API does not scale (softmax_scale = 1): the caller pre-scales q
+    qkv = qkv.bfloat16()
+    g_out = torch.randn(G, L, D).bfloat16()
+    out, dqkv = run_packed(qkv, g_out, torch.bfloat16, dropout_p=0.3, dropout_seed=99)
+    keep, drop_scale = ao.dropout_keep_mask(99, G, L, L, 0.3)
+    x = qkv.float()
+    ref = _dropout_reference(x[0][None], x[1][None], x[2][None], g_out.float()[None], keep[None], drop_scale, True, 0, 1.0)
+    assert rel_fro(out.double(), ref[0][0]) < 1e-2
+    for t in range(3):
+        assert rel_fro(dqkv[t].double(), ref[2 + t][0]) < 1e-2
+    # fp32 / odd head dims keep the reference's refusal
+    with pytest.raises(NotImplementedError, match="dropout_p"):
+        mod._sdpa_impl(None, torch.randn(1, 2, 64, 32, device="cuda"), torch.randn(1, 2, 64, 32, device="cuda"),
+                       torch.randn(1, 2, 64, 32, device="cuda"), None, 0.1, True)
