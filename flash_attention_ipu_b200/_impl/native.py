@@ -18,7 +18,7 @@ EXPORTED_SYMBOLS = (
     "fa_b200_fwd", "fa_b200_bwd", "fa_b200_bwd_workspace_bytes", "fa_b200_bwd_dq_accum", "fa_b200_bwd_noalloc", "fa_b200_bwd_sm_clock",
     "fa_b200_merge",
     "fa_b200_merge_acc",
-    "fa_b200_kernel_family", "fa_b200_set_deterministic", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
+    "fa_b200_kernel_family", "fa_b200_dropout_keep_host", "fa_b200_set_deterministic", "fa_b200_launch_count", "fa_b200_tmap_cache_stats", "fa_b200_last_error",
     "fa_b200_version",
 )
 
@@ -54,6 +54,8 @@ _lib.fa_b200_merge.restype = c_int
 _lib.fa_b200_merge_acc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64,
                                    c_int32, c_int32, c_void_p]
 _lib.fa_b200_merge_acc.restype = c_int
+_lib.fa_b200_dropout_keep_host.argtypes = [_PP, c_int32, c_int32, c_int32, c_int32, c_void_p, POINTER(c_float)]
+_lib.fa_b200_dropout_keep_host.restype = c_int
 _lib.fa_b200_set_deterministic.argtypes = [c_int]
 _lib.fa_b200_set_deterministic.restype = c_int
 _lib.fa_b200_kernel_family.argtypes = [_PP]
@@ -129,6 +131,17 @@ def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
     return Problem(B, H, Lq, k.shape[2], D, _DTYPES[q.dtype], int(bool(causal)), float(scale),
                    int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv, lens_ptr,
                    float(dropout_p), int(dropout_seed) & 0xFFFFFFFFFFFFFFFF)
+
+
+def dropout_keep_host(prob: Problem, group: int, q_row: int, k_first: int = 0, n: "int | None" = None):
+    """(keep, scale): the dropout mask bits of keys ``k_first .. k_first + n`` of one query row, computed on the
+    host by the functions the kernels compile; ``keep`` is a uint8 CPU tensor."""
+    n = prob.Lk - k_first if n is None else n
+    keep = torch.empty(n, dtype=torch.uint8)
+    scale = c_float(0.0)
+    _check(_lib.fa_b200_dropout_keep_host(byref(prob), group, q_row, k_first, n, keep.data_ptr(), byref(scale)),
+           "fa_b200_dropout_keep_host")
+    return keep, float(scale.value)
 
 
 def kernel_family(prob: Problem) -> int:

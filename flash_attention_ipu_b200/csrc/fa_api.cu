@@ -747,4 +747,21 @@ int fa_b200_bwd_noalloc(const fa_b200_problem *p, const fa_b200_tensor *q, const
   return fa_b200_bwd(p, q, k, v, o, dout, lse, dq, dk, dv, scratch, (size_t)FA_B200_NOALLOC_SCRATCH_BYTES, stream);
 }
 
+int fa_b200_dropout_keep_host(const fa_b200_problem *p, int32_t group, int32_t q_row, int32_t k_first, int32_t n,
+                              uint8_t *keep, float *scale) {
+  if (int rc = check_problem(p)) return rc;
+  if (!keep || n < 0 || group < 0 || group >= p->B * p->H || q_row < 0 || q_row >= p->Lq || k_first < 0 ||
+      (int64_t)k_first + n > p->Lk)
+    return fail(FA_B200_ERR_INVALID, "bad dropout_keep_host arguments");
+  const uint32_t th = drop_thresh(p);
+  const uint32_t seed_g = fa::drop_seed_of_group(drop_seed32(p), (uint32_t)group);
+  for (int32_t c = 0; c < n; ++c) {
+    const uint32_t k = (uint32_t)(p->kv_pos0 + k_first + c);
+    const uint32_t h = fa::drop_hash(seed_g, (uint32_t)(p->q_pos0 + q_row), k >> 2);
+    keep[c] = ((h >> ((k & 3u) * 8u)) & 0xffu) >= th ? 1 : 0;
+  }
+  if (scale) *scale = drop_scale(p);
+  return 0;
+}
+
 }  // extern "C"

@@ -153,6 +153,14 @@ int fa_b200_merge_acc(float *o_acc, float *lse_acc, const void *o_b, const float
  * the previous setting.  (dK, dV and the forward are deterministic either way.) */
 int fa_b200_set_deterministic(int on);
 
+/* The dropout mask of a problem, evaluated on the HOST with the very functions the kernels compile
+ * (csrc/sm100_ptx.cuh: drop_hash): keep[c] = 1 iff key k_first + c of query row q_row of group
+ * (b*H + h) survives; *scale (optional) = the factor applied to the survivors.  No reference
+ * counterpart (the reference refuses dropout); for debugging and to pin the CPU oracle's restatement
+ * of the hash without a GPU (tests/test_oracle.py).  No device work. */
+int fa_b200_dropout_keep_host(const fa_b200_problem *p, int32_t group, int32_t q_row, int32_t k_first, int32_t n,
+                              uint8_t *keep, float *scale);
+
 /* Which kernel family a problem dispatches to: 1 = tcgen05/TMA sm_100a kernels,
  * 0 = generic SIMT kernels (fp32 inputs / head dims the tensor path does not cover),
  * negative = unsupported. */

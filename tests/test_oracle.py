@@ -88,3 +88,31 @@ def test_heuristic_chunks():
     assert ao.heuristic_chunks(8192, 128) == (8, 8)
     assert ao.heuristic_chunks(512, 64) == (4, 2)
     assert ao.heuristic_chunks(64, 128) == (1, 1)
+
+
+@pytest.mark.parametrize("seed,p_drop,q0,k0", [(0, 0.25, 0, 0), (0x1234_5678_9ABC_DEF1, 0.1, 128, 0),
+                                               (2 ** 63 + 12345, 0.5, 0, 64), (99, 0.003, 7, 4)])
+def test_dropout_mask_restatement_matches_the_library(seed, p_drop, q0, k0):
+    """oracle/attention_oracle.py: dropout_keep_mask against fa_b200_dropout_keep_host, which evaluates the
+    functions the kernels compile (csrc/sm100_ptx.cuh: drop_hash) on the host: pins the restatement of the
+    hash, the threshold and the scale without a GPU.  (Against the REFERENCE it stays unpinned: the
+    reference has no dropout.)"""
+    from flash_attention_ipu_b200._impl import native
+    B, H, Lq, Lk, D = 2, 3, 37, 203, 64
+    prob = native.Problem(B, H, Lq, Lk, D, native.FA_B200_BF16, 1, 0.125, 0, 0, q0, k0, 0, None, p_drop,
+                          seed & 0xFFFFFFFFFFFFFFFF)
+    keep, scale = ao.dropout_keep_mask(seed, B * H, Lq, Lk, p_drop, q0, k0)
+    for g in range(B * H):
+        for r in (0, 1, Lq // 2, Lq - 1):
+            got, got_scale = native.dropout_keep_host(prob, g, r)
+            assert torch.equal(got.bool(), keep[g, r]), (g, r)
+            assert abs(got_scale - scale) < 1e-6
+    part, _ = native.dropout_keep_host(prob, 1, 5, 10, 50)
+    assert torch.equal(part.bool(), keep[1, 5, 10:60])
+    frac = keep.float().mean().item()
+    thresh = max(1, round(p_drop * 256))
+    assert abs(frac - (1 - thresh / 256)) < 0.02
+    # rows, groups and seeds decorrelate
+    assert not torch.equal(keep[0, 0], keep[0, 1]) and not torch.equal(keep[0], keep[1])
+    other, _ = ao.dropout_keep_mask(seed + 1, B * H, Lq, Lk, p_drop, q0, k0)
+    assert not torch.equal(other, keep)
