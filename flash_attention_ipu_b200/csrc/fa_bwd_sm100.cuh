@@ -48,9 +48,13 @@ namespace fa {
 
 constexpr int kBwdThreads = 512;
 #ifndef FA_BWD_POLY_PAIRS
-#define FA_BWD_POLY_PAIRS 12
+#define FA_BWD_POLY_PAIRS 4
 #endif
-constexpr int kBwdPolyPairs = FA_BWD_POLY_PAIRS;  // of a thread's 32 pairs of exponentials, how many run on the FMA pipe
+// of a thread's 32 pairs of exponentials, how many run on the FMA pipe.  12 gives the fewest cycles (7.31 M on
+// config 3), but the pool's B200s run this kernel AT THEIR 1000 W CAP, where the polynomial's ~10 FMA-pipe
+// instructions per pair cost more energy than one MUFU op: 0 / 4 pairs measure 968-971 TFLOP/s, 8 / 12 pairs
+// 940-946 (profiles/r02_power_probe_poly.log; sustained >= 1.5 s legs, alternating builds)
+constexpr int kBwdPolyPairs = FA_BWD_POLY_PAIRS;
 constexpr int kBwdRegCompute = 144, kBwdRegDrain = 152, kBwdRegOther = 72;  // 8x32x144 + 4x32x152 + 4x32x72 = 65536
 constexpr int kBwdConsumerWarps = 13;             // compute 8 + drain 4 + MMA 1 read every scheduled item
 
