@@ -109,6 +109,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+#ifndef FA_TMAP_L2_PROMOTION  // L2 sector promotion of TMA loads (probe at the power cap: profiles/r02_power_probe_l2.log)
+#define FA_TMAP_L2_PROMOTION CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+#endif
 EncodeTiledFn encode_fn() {
   static EncodeTiledFn fn = [] {
     void *sym = nullptr;
@@ -202,7 +205,7 @@ int make_tmap(CUtensorMap *m, const fa_b200_tensor *t, int dtype, int B, int H, 
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, dt, 4, t->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   box_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  FA_TMAP_L2_PROMOTION,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(FA_B200_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
   tmap_insert(key, *m);
