@@ -5,6 +5,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <type_traits>
@@ -41,6 +42,31 @@ int launched() {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(FA_B200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
   return 0;
+}
+
+// Programmatic dependent launch for the tensor family's four kernels (forward, prep, backward, convert):
+// each may be placed on SMs the kernel ahead of it in the stream has already left and runs its prologue
+// there; it waits (griddepcontrol.wait) before touching global memory.  FA_B200_PDL=0 turns it off.
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char *e = getenv("FA_B200_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+void launch_pdl(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st, Args &&...args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);  // errors surface through launched()
 }
 
 size_t elem_size(int dtype) { return dtype == FA_B200_F32 ? 4 : 2; }
@@ -428,7 +454,7 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
     if (rc) return rc;
   }
   const unsigned grid = (unsigned)(items < sms ? items : sms);
-  kern<<<grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st>>>(tq, tk, tv, to, fp);
+  launch_pdl(kern, grid, fa::kFwdThreads, fa::FwdSmem<D>::kAlloc, st, tq, tk, tv, to, fp);
   return launched();
 }
 
@@ -459,10 +485,10 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   int *counter = reinterpret_cast<int *>(ws + 2 * ws_stat_bytes(p) + ws_acc_bytes(p));
   int *dq_sem = g_deterministic.load(std::memory_order_relaxed) ? reinterpret_cast<int *>(ws + 2 * ws_stat_bytes(p) + ws_acc_bytes(p) + 256) : nullptr;
   const int G = p->B * p->H, Lp = lq_pad(p);
-  fa::fa_bwd_prep_kernel<T, D><<<blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st>>>(
-      reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
-      reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
-      delta, lse2, dq_accum ? nullptr : dq_acc, p->B, p->H, p->Lq, Lp, counter, dq_sem, (int)ws_sem_count(p));
+  launch_pdl(fa::fa_bwd_prep_kernel<T, D>, blocks_for((int64_t)G * Lp, 256 / (D / 8)), 256, 0, st,
+             reinterpret_cast<const T *>(o->ptr), o->stride_b, o->stride_h, o->stride_l,
+             reinterpret_cast<const T *>(dout->ptr), dout->stride_b, dout->stride_h, dout->stride_l, lse,
+             delta, lse2, dq_accum ? nullptr : dq_acc, p->B, p->H, p->Lq, Lp, counter, dq_sem, (int)ws_sem_count(p));
   if (int rc = launched()) return rc;
 
   fa_b200_tensor acc{dq_acc, (int64_t)p->H * p->Lq * D, (int64_t)p->Lq * D, (int64_t)D};
@@ -504,7 +530,7 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   cudaMemset(d_btrace, 0, 16 * 8);
   bp.trace = d_btrace;
 #endif
-  kern<<<grid, fa::kBwdThreads, fa::BwdSmem<D>::kBytes, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, bp);
+  launch_pdl(kern, grid, fa::kBwdThreads, fa::BwdSmem<D>::kBytes, st, tq, tk, tv, tdo, tdq, tdk, tdv, bp);
   if (int rc = launched()) return rc;
 #ifdef FA_BWD_TRACE
   if (D == 128 && p->Lq >= 8192) {
@@ -518,8 +544,8 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
 #endif
   if (dq_accum) return 0;
   // dQ = softmax_scale * dq_acc, cast to the output dtype
-  fa::fa_convert_kernel<T><<<148 * 8, 256, 0, st>>>(dq_acc, view<T>(dq), p->B, p->H, p->Lq, D,
-                                                     p->softmax_scale);
+  launch_pdl(fa::fa_convert_kernel<T>, 148 * 8, 256, 0, st, static_cast<const float *>(dq_acc), view<T>(dq), p->B, p->H,
+             p->Lq, D, p->softmax_scale);
   return launched();
 }
 

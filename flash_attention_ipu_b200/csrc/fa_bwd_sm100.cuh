@@ -212,6 +212,8 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  griddep_launch_dependents();
+  griddep_wait();  // nothing above touched global memory (sm100_ptx.cuh: programmatic dependent launch)
 
   // Every consumer warp fetches item number `k` of this CTA the same way: wait for the slot, read
   // it, and tell the producer the slot may be reused (item k + 2).
@@ -695,6 +697,8 @@ fa_bwd_prep_kernel(const T *o, int64_t o_sb, int64_t o_sh, int64_t o_sl, const T
                    int64_t d_sh, int64_t d_sl, const float *lse, float *delta, float *lse2,
                    float *dq_acc, int B, int H, int Lq, int Lq_pad, int *sched_counter, int *dq_sem, int sem_count) {
   constexpr int kTpr = D / 8;  // threads per row
+  griddep_launch_dependents();
+  griddep_wait();
   if (blockIdx.x == 0 && threadIdx.x == 0) *sched_counter = 0;
   if (dq_sem)
     for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < sem_count;

@@ -178,6 +178,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  griddep_launch_dependents();
+  griddep_wait();  // nothing above touched global memory (sm100_ptx.cuh: programmatic dependent launch)
 
   // every consumer warp fetches item number `k` of this CTA the same way
   auto next_item = [&](int k) -> int {

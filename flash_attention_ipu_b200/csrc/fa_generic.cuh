@@ -305,6 +305,9 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 fa_convert_kernel(const float *src, View<T> dst, int B, int H, int L, int D, float scale) {
   static_assert(sizeof(T) == 2, "16-bit outputs only (8 elements = one 16-byte store)");
+  // programmatic dependent launch (see sm100_ptx.cuh): no-ops when launched the plain way
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const int64_t n8 = static_cast<int64_t>(B) * H * L * D / 8;  // D is 64 or 128 on this path
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {

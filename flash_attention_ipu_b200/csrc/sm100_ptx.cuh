@@ -530,6 +530,17 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   return r;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may be scheduled before
+// the kernel ahead of it in the stream has finished: its CTAs run their prologue (barrier init, TMEM
+// allocation, descriptor prefetch) on SMs the earlier kernel has already left, and must execute
+// griddep_wait() before they touch any global memory (it returns once the earlier grid has completed
+// and its writes are visible).  griddep_launch_dependents() tells the scheduler that the NEXT kernel
+// may start being placed; every CTA calls it right at the start, so the next grid is placed only once
+// every CTA of this one is resident or done.  Both are no-ops in a kernel launched the plain way.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- dropout (counter-based, no state)
 // One 32-bit hash decides FOUR neighbouring keys of one query: byte b of drop_hash(seed_g, q, k >> 2)
 // belongs to key k (b = k & 3), and the key is KEPT iff that byte >= thresh (thresh = round(256 p),

@@ -116,7 +116,9 @@ def test_chunk_hints_do_not_change_the_result(dtype):
     for ncq, nckv in [(2, 2), (4, 2), (2, 4), (8, 8), (512, 256)]:
         got = run_packed(qkv, grad, DT[dtype], ncq, nckv)
         assert torch.equal(got[0], base[0])
-        assert rel_fro(got[1], base[1]) < 1e-5  # dQ accumulates by atomics: order may differ
+        # dQ accumulates by fp32 reduce-adds in arrival order: a sum may round to the neighbouring 16-bit value
+        # (one such flip among 65 536 elements is already 1.5e-5 relative Frobenius)
+        assert rel_fro(got[1], base[1]) < 1e-3
 
 
 @pytest.mark.parametrize("G,L,D", [(2, 200, 128), (1, 8, 64), (3, 331, 64), (1, 129, 128), (2, 1, 64)])
@@ -747,7 +749,8 @@ def test_kv_lens_packed_api_and_skipped_tiles():
         o1, _ = ops.attention_fwd(q1, k1[:, :, :m], v1[:, :, :m], 1.0, False, 0, 0)
         o1.backward(g[n][None, None])
         assert torch.equal(o1[0, 0], out[n])
-        assert rel_fro(x.grad[0, n].float(), q1.grad[0, 0].float()) < 1e-5
+        # dQ: fp32 partials added in arrival order, then rounded to bf16 -- single-ulp flips are legitimate
+        assert rel_fro(x.grad[0, n].float(), q1.grad[0, 0].float()) < 1e-3
         assert torch.equal(x.grad[1, n, :m], k1.grad[0, 0, :m]) and torch.equal(x.grad[2, n, :m], v1.grad[0, 0, :m])
         assert torch.count_nonzero(x.grad[1:, n, m:]) == 0
 
