@@ -382,12 +382,14 @@ int sm_count() {  // per device: a process may drive several GPUs
 }
 
 // Work counters of the persistent forward (the backward keeps its counter in its workspace; the
-// forward has none).  A ring of kFwdCounters 4-byte slots per device in a static device array (the
-// library allocates nothing; address looked up once per device with that device current); every launch
-// takes the next slot and zeroes it ON ITS STREAM right before the kernel, so launches on different
-// streams never share a counter unless kFwdCounters of them are in flight at once.
+// forward has none).  A ring of kFwdCounters 8-byte slots per device in a static, zero-initialised device
+// array (the library allocates nothing; address looked up once per device with that device current).
+// Every launch takes the next slot; the kernel itself leaves the slot zeroed when its last CTA has
+// stopped claiming work (fa_fwd_sm100.cuh), so no memset sits between a forward and the kernel ahead of
+// it in the stream, and launches on different streams never share a counter unless kFwdCounters of
+// them are in flight at once.
 constexpr int kFwdCounters = 1024;
-static __device__ __align__(256) int g_fwd_counters[kFwdCounters];  // host code: a symbol, not an address
+static __device__ __align__(256) int g_fwd_counters[2 * kFwdCounters];  // host code: a symbol, not an address
 int *fwd_counter_slot(cudaStream_t st, int *rc) {
   static std::atomic<int *> base[64];
   static std::atomic<unsigned> next{0};
@@ -407,12 +409,8 @@ int *fwd_counter_slot(cudaStream_t st, int *rc) {
       base[dev & 63].store(b, std::memory_order_release);
     }
   }
-  int *slot = b + next.fetch_add(1, std::memory_order_relaxed) % kFwdCounters;
-  if (cudaMemsetAsync(slot, 0, sizeof(int), st) != cudaSuccess) {
-    *rc = fail(FA_B200_ERR_CUDA, "cudaMemsetAsync of the forward work counter failed");
-    return nullptr;
-  }
-  return slot;
+  (void)st;
+  return b + 2 * (next.fetch_add(1, std::memory_order_relaxed) % kFwdCounters);
 }
 
 template <int D, bool kBf16>

@@ -69,7 +69,8 @@ constexpr int kFwdConsumerWarps = 9;       // 8 softmax warps + the MMA warp rea
 struct FwdParams {
   float *lse;         // [G][Lq] fp32
   const int *kv_lens; // [B*H] keys of each (batch, head) that exist (<= Lk; the rest is padding), or nullptr
-  int *sched_counter; // zeroed before the launch; next unclaimed item = gridDim.x + counter.  nullptr: grid = items
+  int *sched_counter; // [2], both zero at launch: [0] next unclaimed item - gridDim.x, [1] CTAs that are done claiming;
+                      // the last of them zeroes both again (no memset between launches).  nullptr: grid = items
   int Lq, Lk, H;      // H: heads per batch (group g -> (b = g / H, h = g % H))
   int kv_ratio;       // query heads per K/V head (1 = multi-head; >1 = grouped-query attention)
   int causal;
@@ -201,7 +202,18 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_wait(&sched_empty[s], ((k >> 1) & 1) ^ 1);
         sched_item[s] = w < p.num_items ? w : -1;
         mbar_arrive(&sched_full[s]);
-        if (w >= p.num_items) break;
+        if (w >= p.num_items) {
+          // this CTA will not touch the work counter again; the last CTA to get here leaves it zeroed
+          // for the next launch that is handed this slot (stream order separates the two launches)
+          if (p.sched_counter) {
+            __threadfence();
+            if (atomicAdd(p.sched_counter + 1, 1) == static_cast<int>(gridDim.x) - 1) {
+              p.sched_counter[0] = 0;
+              p.sched_counter[1] = 0;
+            }
+          }
+          break;
+        }
         const FwdItem t = fwd_decode(p, w);
         w = p.sched_counter ? gridDim.x + atomicAdd(p.sched_counter, 1) : p.num_items;
         if (t.n_max == 0) continue;
