@@ -369,6 +369,25 @@ int generic_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200
 }
 
 // ---------------------------------------------------------------- tensor family: forward
+// Item order of the persistent kernels.  Causal items cost between 1 and Lk / 128 tile steps; handed out
+// group by group (heaviest first inside a group) the launch ends with whatever the last groups still have
+// running, up to one full-length item per SM.  So the (batch, K/V head) groups are walked in CHUNKS whose
+// K + V (forward) stay L2-resident, and inside a chunk the heaviest items of all its groups come first:
+// every chunk, and so the launch, ends with its lightest items, while the next chunk's heavy items are
+// already running.  GPT-2-small shape (384 forward items of 2-8 steps on 148 SMs, one chunk): 0.134 ->
+// 0.118 ms per fwd+bwd.  One global order on config 3 (K + V = 537 MB) instead: 1 109 -> 894 forward,
+// 920 -> 622 backward TFLOP/s -- the chunk must fit in L2.  Non-causal items all cost the same: 1.
+#ifndef FA_ORDER_CHUNK_BYTES
+#define FA_ORDER_CHUNK_BYTES (32ll << 20)
+#endif
+int order_chunk(const fa_b200_problem *p) {
+  if (!p->causal) return 1;
+  const int64_t group_kv_bytes = 2 * (int64_t)p->Lk * p->D * 2, groups = (int64_t)p->B * kv_heads(p);
+  int64_t cg = (long long)FA_ORDER_CHUNK_BYTES / (group_kv_bytes > 0 ? group_kv_bytes : 1);
+  cg = cg < 1 ? 1 : cg > groups ? groups : cg;
+  return (int)cg;
+}
+
 int sm_count() {  // per device: a process may drive several GPUs
   static std::atomic<int> cached[64];
   int dev = 0;
@@ -433,6 +452,7 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const int64_t items = (int64_t)p->B * p->H * fp.num_pairs;
   if (items > INT32_MAX) return fail(FA_B200_ERR_UNSUPPORTED, "too many Q tile pairs (%lld)", (long long)items);
   fp.num_items = (int)items;
+  fp.order_chunk = order_chunk(p);
   const bool drop = drop_thresh(p) > 0;
   fp.drop_thresh4 = drop_thresh(p) * 0x01010101u;
   fp.drop_seed = drop_seed32(p);
@@ -510,6 +530,8 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const int64_t items = (int64_t)p->B * Hkv * bp.num_kv_tiles;  // one work item per (batch, K/V head, KV tile)
   if (items > INT32_MAX) return fail(FA_B200_ERR_UNSUPPORTED, "too many KV tiles (%lld)", (long long)items);
   bp.num_items = (int)items;
+  // deterministic dQ needs the group-major descending order (a CTA waits for a tile claimed before its own)
+  bp.order_chunk = dq_sem ? 1 : order_chunk(p);
   const bool gqa = bp.kv_ratio > 1, drop = drop_thresh(p) > 0;
   bp.drop_thresh4 = drop_thresh(p) * 0x01010101u;
   bp.drop_seed = drop_seed32(p);

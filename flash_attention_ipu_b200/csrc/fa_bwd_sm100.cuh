@@ -73,6 +73,8 @@ struct BwdParams {
   float scale, scale_log2;
   int num_kv_tiles;    // ceil(Lk / 128)
   int num_items;       // B * Hkv * num_kv_tiles
+  int order_chunk;     // groups per scheduling chunk (FwdParams::order_chunk): inside a chunk the KV tiles with most
+                       // Q tiles of all its groups come first.  1 = group-major
   // dropout (kDrop instantiation only), as in FwdParams: the same hash regenerates the forward's mask
   uint32_t drop_thresh4, drop_seed;
   float drop_scale;
@@ -117,12 +119,17 @@ struct BwdItem {
 template <bool kGqa>
 __device__ __forceinline__ BwdItem bwd_decode(const BwdParams &p, int w, int num_q_tiles) {
   BwdItem t;
-  const int gk = w / p.num_kv_tiles;
+  const int gks = p.num_items / p.num_kv_tiles;
+  const int chunk = w / (p.order_chunk * p.num_kv_tiles);
+  const int g0 = chunk * p.order_chunk, gc = min(p.order_chunk, gks - g0);  // the last chunk may be short
+  const int r = w - g0 * p.num_kv_tiles;
+  const int gk = g0 + r % gc;
+  const int jw = r / gc;
   // ascending: the KV tiles with most Q tiles first.  Deterministic dQ: DESCENDING, because the
   // partials of a Q tile are then added in descending KV-tile order and the tile a CTA waits for
   // must have been claimed before its own (it is then running or done: no deadlock, and it reaches
   // every shared Q tile one iteration earlier, so the wait is normally already satisfied)
-  t.j = p.dq_sem ? p.num_kv_tiles - 1 - (w % p.num_kv_tiles) : w % p.num_kv_tiles;
+  t.j = p.dq_sem ? p.num_kv_tiles - 1 - jw : jw;
   t.b = gk / p.Hkv;
   t.hk = gk % p.Hkv;
   t.i0 = bwd_first_q_tile(p, t.j);

@@ -78,6 +78,9 @@ struct FwdParams {
   float scale_log2;   // softmax_scale * log2(e)
   int num_pairs;      // ceil(Lq / 256)
   int num_items;      // B * H * num_pairs
+  int order_chunk;    // item order: the groups are walked in chunks of this many (K + V of a chunk stay in L2), and
+                      // inside a chunk the heaviest pairs of ALL its groups come first, so that a chunk -- and the
+                      // whole launch -- ends with its lightest items.  1 = group-major, >= groups = one global order
   // dropout on P (kDrop instantiation only; sm100_ptx.cuh: drop_hash): keep key iff its hash byte >= thresh
   uint32_t drop_thresh4;  // thresh * 0x01010101
   uint32_t drop_seed;     // 32-bit fold of fa_b200_problem.dropout_seed
@@ -118,8 +121,12 @@ struct FwdItem {
 };
 __device__ __forceinline__ FwdItem fwd_decode(const FwdParams &p, int w) {
   FwdItem t;
-  t.g = w / p.num_pairs;
-  const int pair = p.num_pairs - 1 - (w % p.num_pairs);
+  const int groups = p.num_items / p.num_pairs;
+  const int chunk = w / (p.order_chunk * p.num_pairs);
+  const int g0 = chunk * p.order_chunk, gc = min(p.order_chunk, groups - g0);  // the last chunk may be short
+  const int r = w - g0 * p.num_pairs;
+  t.g = g0 + r % gc;
+  const int pair = p.num_pairs - 1 - r / gc;
   t.b = t.g / p.H;
   t.h = t.g % p.H;
   t.t0 = 2 * pair;
