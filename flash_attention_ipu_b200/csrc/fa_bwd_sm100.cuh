@@ -47,6 +47,19 @@
 namespace fa {
 
 constexpr int kBwdThreads = 512;
+// L2 eviction hints of the backward's TMA traffic (0 none, 1 evict_first, 2 evict_last), probed at the power cap
+#ifndef FA_BWD_HINT_KV
+#define FA_BWD_HINT_KV 0   // K / V tiles: read once per item
+#endif
+#ifndef FA_BWD_HINT_Q
+#define FA_BWD_HINT_Q 0    // Q / dO tiles: re-read by every KV tile of the group
+#endif
+#ifndef FA_BWD_HINT_DQ
+#define FA_BWD_HINT_DQ 0   // fp32 dQ partial sums: re-touched by every KV tile of the group
+#endif
+#ifndef FA_BWD_HINT_OUT
+#define FA_BWD_HINT_OUT 0  // dK / dV: written once
+#endif
 #ifndef FA_BWD_POLY_PAIRS
 #define FA_BWD_POLY_PAIRS 4
 #endif
@@ -264,22 +277,22 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           mbar_wait(&q_empty[st], ((git >> 1) & 1) ^ 1);
           mbar_arrive_expect_tx(&q_full[st], L::kTileBytes + 1024);
           for (int hh = 0; hh < kHalves; ++hh)
-            tma_load_4d(&tmQ, &q_full[st], smem + L::kQOff + st * L::kTileBytes + hh * L::kHalfBytes,
-                        hh * 64, i * 128, h, t.b);
+            tma_load_4d_h<FA_BWD_HINT_Q>(&tmQ, &q_full[st], smem + L::kQOff + st * L::kTileBytes + hh * L::kHalfBytes,
+                                         hh * 64, i * 128, h, t.b);
           bulk_load_1d(smem + L::kStatOff + st * 1024, lse_g + i * 128, 512, &q_full[st]);
           bulk_load_1d(smem + L::kStatOff + st * 1024 + 512, delta_g + i * 128, 512, &q_full[st]);
           mbar_wait(do_empty, (git & 1) ^ 1);
           mbar_arrive_expect_tx(do_full, L::kTileBytes);
           for (int hh = 0; hh < kHalves; ++hh)
-            tma_load_4d(&tmDO, do_full, smem + L::kDOOff + hh * L::kHalfBytes, hh * 64, i * 128, h, t.b);
+            tma_load_4d_h<FA_BWD_HINT_Q>(&tmDO, do_full, smem + L::kDOOff + hh * L::kHalfBytes, hh * 64, i * 128, h, t.b);
           if (it == 0) {
             // K, V after the first Q / dO tiles: those only need a free ring stage, K / V need the
             // previous item's last MMAs to have completed
             if (kc > 0) mbar_wait(dkv_full, (kc - 1) & 1);
             mbar_arrive_expect_tx(kv_full, 2 * L::kTileBytes);
             for (int hh = 0; hh < kHalves; ++hh) {
-              tma_load_4d(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
-              tma_load_4d(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
+              tma_load_4d_h<FA_BWD_HINT_KV>(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
+              tma_load_4d_h<FA_BWD_HINT_KV>(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
             }
           }
         }
@@ -454,7 +467,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           __syncwarp();
           if (lane == 0) {
 #ifndef FA_EXPERIMENT_NO_REDUCE  // timing / power experiment only when defined (wrong results; needs FA_ALLOW_EXPERIMENTS)
-            tma_reduce_add_4d(&tmDQ, slab, c * 32, i * 128 + wq * 32, h, t.b);
+            tma_reduce_add_4d_h<FA_BWD_HINT_DQ>(&tmDQ, slab, c * 32, i * 128 + wq * 32, h, t.b);
 #endif
             tma_store_commit();
           }
@@ -668,10 +681,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           if (D == 128) {
             const CUtensorMap *tm = round == 0 ? &tmDK : &tmDV;
             for (int hh = 0; hh < 2; ++hh)
-              tma_store_4d(tm, smem + L::kDSOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
+              tma_store_4d_h<FA_BWD_HINT_OUT>(tm, smem + L::kDSOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
           } else {
-            tma_store_4d(&tmDK, smem + L::kDSOff, 0, t.j * 128, t.hk, t.b);
-            tma_store_4d(&tmDV, smem + L::kDSOff + L::kHalfBytes, 0, t.j * 128, t.hk, t.b);
+            tma_store_4d_h<FA_BWD_HINT_OUT>(&tmDK, smem + L::kDSOff, 0, t.j * 128, t.hk, t.b);
+            tma_store_4d_h<FA_BWD_HINT_OUT>(&tmDV, smem + L::kDSOff + L::kHalfBytes, 0, t.j * 128, t.hk, t.b);
           }
           tma_store_commit();
           tma_store_wait_read<0>();  // the buffer is written again (next round / next item's dS^T)

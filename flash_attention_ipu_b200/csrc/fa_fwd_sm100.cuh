@@ -41,6 +41,12 @@ namespace fa {
 constexpr int kBlockM = 128;     // query rows per Q tile (= TMEM lanes)
 constexpr int kBlockN = 128;     // keys per KV tile
 constexpr int kFwdThreads = 384;
+#ifndef FA_FWD_HINT_Q
+#define FA_FWD_HINT_Q 0    // L2 eviction hints (sm100_ptx.cuh): Q tiles are read once,
+#endif
+#ifndef FA_FWD_HINT_OUT
+#define FA_FWD_HINT_OUT 0  // O is written once
+#endif
 #ifndef FA_FWD_K_STAGES
 #define FA_FWD_K_STAGES 3
 #endif
@@ -228,8 +234,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           mbar_wait(&q_empty[i], (kq & 1) ^ 1);  // the previous item's S_i products have read the buffer
           mbar_arrive_expect_tx(&q_full[i], L::kTileBytes);
           for (int hh = 0; hh < kHalves; ++hh)
-            tma_load_4d(&tmQ, &q_full[i], smem + L::kQOff + i * L::kTileBytes + hh * L::kHalfBytes,
-                        hh * 64, (t.t0 + i) * kBlockM, t.h, t.b);
+            tma_load_4d_h<FA_FWD_HINT_Q>(&tmQ, &q_full[i], smem + L::kQOff + i * L::kTileBytes + hh * L::kHalfBytes,
+                                         hh * 64, (t.t0 + i) * kBlockM, t.h, t.b);
         }
         ++kq;
         for (int j = 0; j < t.n_max; ++j, ++kj) {
@@ -495,7 +501,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if ((warp & 3) == 0 && lane == 0) {
           if ((t.t0 + i) * kBlockM < p.Lq) {
             for (int hh = 0; hh < kHalves; ++hh)
-              tma_store_4d(&tmO, o_smem + hh * L::kHalfBytes, hh * 64, (t.t0 + i) * kBlockM, t.h, t.b);
+              tma_store_4d_h<FA_FWD_HINT_OUT>(&tmO, o_smem + hh * L::kHalfBytes, hh * 64, (t.t0 + i) * kBlockM, t.h, t.b);
             tma_store_commit();
             tma_store_wait_read<0>();
           }

@@ -127,6 +127,40 @@ __device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap *m, const vo
       "r"(c3)
       : "memory");
 }
+// The same three operations with an L2 eviction-priority hint (kHint: 0 none, 1 evict_first, 2 evict_last;
+// the 64-bit policies are the fixed encodings createpolicy.fractional produces for fraction 1.0)
+template <int kHint> __device__ __forceinline__ uint64_t l2_policy() {
+  return kHint == 1 ? 0x12F0000000000000ull : 0x14F0000000000000ull;
+}
+template <int kHint>
+__device__ __forceinline__ void tma_load_4d_h(const CUtensorMap *m, uint64_t *bar, void *dst, int c0, int c1, int c2, int c3) {
+  if (kHint == 0) { tma_load_4d(m, bar, dst, c0, c1, c2, c3); return; }
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0),
+      "r"(c1), "r"(c2), "r"(c3), "l"(l2_policy<kHint>())
+      : "memory");
+}
+template <int kHint>
+__device__ __forceinline__ void tma_store_4d_h(const CUtensorMap *m, const void *src, int c0, int c1, int c2, int c3) {
+  if (kHint == 0) { tma_store_4d(m, src, c0, c1, c2, c3); return; }
+  asm volatile(
+      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3, %4, %5}], [%1], %6;"
+      ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2),
+      "r"(c3), "l"(l2_policy<kHint>())
+      : "memory");
+}
+template <int kHint>
+__device__ __forceinline__ void tma_reduce_add_4d_h(const CUtensorMap *m, const void *src, int c0, int c1, int c2, int c3) {
+  if (kHint == 0) { tma_reduce_add_4d(m, src, c0, c1, c2, c3); return; }
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.bulk_group.L2::cache_hint"
+      " [%0, {%2, %3, %4, %5}], [%1], %6;"
+      ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2),
+      "r"(c3), "l"(l2_policy<kHint>())
+      : "memory");
+}
 // pull one box of a tiled tensor into L2 (no shared-memory destination, no completion to wait for)
 __device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap *m, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
