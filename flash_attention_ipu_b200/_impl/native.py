@@ -33,6 +33,7 @@ class Problem(Structure):  # fa_b200_problem
         ("dtype", c_int32), ("causal", c_int32), ("softmax_scale", c_float),
         ("block_q_hint", c_int32), ("block_kv_hint", c_int32), ("q_pos0", c_int32), ("kv_pos0", c_int32),
         ("H_kv", c_int32), ("kv_lens", c_void_p), ("dropout_p", c_float), ("dropout_seed", c_uint64),
+        ("bias", c_void_p), ("bias_stride_b", c_int64), ("bias_stride_h", c_int64), ("bias_stride_l", c_int64),
     ]
 
 
@@ -114,9 +115,23 @@ def _require_cuda(*ts: torch.Tensor) -> None:
             )
 
 
+def _bias_fields(bias, q, k):
+    """(pointer, stride_b, stride_h, stride_l) of an additive score bias broadcastable to (B, H, Lq, Lk)."""
+    if bias is None:
+        return None, 0, 0, 0
+    B, H, Lq, _ = q.shape
+    Lk = k.shape[2]
+    if not (bias.is_cuda and bias.dtype == q.dtype and bias.ndim == 4 and tuple(bias.shape[2:]) == (Lq, Lk)
+            and bias.shape[0] in (1, B) and bias.shape[1] in (1, H) and bias.stride(3) == 1):
+        raise RuntimeError("bias must be a CUDA tensor of q's dtype, shaped (B|1, H|1, Lq, Lk), unit stride on Lk")
+    return (bias.data_ptr(), bias.stride(0) if bias.shape[0] > 1 else 0, bias.stride(1) if bias.shape[1] > 1 else 0,
+            bias.stride(2))
+
+
 def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
                  block_q: int = 0, block_kv: int = 0, q_pos0: int = 0, kv_pos0: int = 0,
-                 kv_lens: "torch.Tensor | None" = None, dropout_p: float = 0.0, dropout_seed: int = 0) -> Problem:
+                 kv_lens: "torch.Tensor | None" = None, dropout_p: float = 0.0, dropout_seed: int = 0,
+                 bias: "torch.Tensor | None" = None) -> Problem:
     if q.dtype not in _DTYPES:
         raise RuntimeError(f"unsupported dtype {q.dtype}")
     B, H, Lq, D = q.shape
@@ -130,7 +145,7 @@ def make_problem(q: torch.Tensor, k: torch.Tensor, causal: bool, scale: float,
         lens_ptr = kv_lens.data_ptr()
     return Problem(B, H, Lq, k.shape[2], D, _DTYPES[q.dtype], int(bool(causal)), float(scale),
                    int(block_q), int(block_kv), int(q_pos0), int(kv_pos0), 0 if H_kv == H else H_kv, lens_ptr,
-                   float(dropout_p), int(dropout_seed) & 0xFFFFFFFFFFFFFFFF)
+                   float(dropout_p), int(dropout_seed) & 0xFFFFFFFFFFFFFFFF, *_bias_fields(bias, q, k))
 
 
 def dropout_keep_host(prob: Problem, group: int, q_row: int, k_first: int = 0, n: "int | None" = None):

@@ -63,12 +63,13 @@ def _like_kernel_view(t):
 
 
 @torch.library.register_fake("flash_attention_ipu::attention_fwd")
-def _(q, k, v, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0):
+def _(q, k, v, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0, bias=None):
     return _like_kernel_view(q), q.new_empty(q.shape[:3], dtype=torch.float32)
 
 
 @torch.library.register_fake("flash_attention_ipu::attention_bwd")
-def _(dout, q, k, v, out, lse, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0):
+def _(dout, q, k, v, out, lse, softmax_scale, causal, block_q, block_kv, kv_lens=None, dropout_p=0.0, dropout_seed=0,
+      bias=None):
     return _like_kernel_view(q), _like_kernel_view(k), _like_kernel_view(v)
 
 

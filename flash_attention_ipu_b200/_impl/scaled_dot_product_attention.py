@@ -21,6 +21,7 @@ from . import ops
 from .utils import patch_function, unpatch_function
 
 _SUPPORTED = (torch.bfloat16, torch.float16, torch.float32)
+KEY_PADDING_FAST_PATH = True  # boolean (B, 1, 1, Lk) masks are taken as prefix (right-padding) masks -> kv_lens
 
 
 def _chunk_heuristic(L: int, D: int):
@@ -48,6 +49,27 @@ def _key_padding_lengths(mask: torch.Tensor, query: torch.Tensor, key: torch.Ten
     return lens.repeat_interleave(H).contiguous()
 
 
+def _additive_bias(mask: torch.Tensor, query: torch.Tensor, key: torch.Tensor):
+    """The mask as an additive score bias the kernels take -- q's dtype, 4-D, broadcastable to
+    (B, H, Lq, Lk), unit stride on the keys -- or None if the problem is off the tensor path.  Boolean
+    masks become 0 / -inf (True = attend, as in torch); float masks are added as they are."""
+    if (query.ndim != 4 or not query.is_cuda or not mask.is_cuda or mask.ndim > 4 or mask.requires_grad
+            or query.dtype not in (torch.bfloat16, torch.float16) or query.shape[-1] not in (64, 128)
+            or key.shape[-2] % 8 != 0):
+        return None
+    B, H, Lq, Lk = query.shape[0], query.shape[1], query.shape[2], key.shape[-2]
+    m = mask.reshape((1,) * (4 - mask.ndim) + tuple(mask.shape))
+    if any(have not in (1, want) for have, want in zip(m.shape, (B, H, Lq, Lk))):
+        return None
+    if m.dtype == torch.bool:
+        m = torch.zeros(m.shape, dtype=query.dtype, device=m.device).masked_fill_(~m, float("-inf"))
+    elif m.dtype != query.dtype:
+        m = m.to(query.dtype)
+    if m.shape[3] != Lk:  # one value for every key: the kernels need unit stride on the keys
+        m = m.expand(m.shape[0], m.shape[1], m.shape[2], Lk).contiguous()
+    return m.expand(m.shape[0], m.shape[1], Lq, Lk)  # a broadcast query dim stays a stride of 0
+
+
 def _sdpa_impl(
     orig_fn: Callable,
     query: torch.Tensor,
@@ -59,17 +81,25 @@ def _sdpa_impl(
     scale: Optional[float] = None,
     enable_gqa: bool = False,
 ) -> torch.Tensor:
-    kv_lens = None
+    kv_lens = bias = None
     if attn_mask is not None:
-        # The reference refuses every mask (:21-24).  Here ONE form is taken: a boolean key-padding
-        # mask, (B, 1, 1, Lk) or (B, Lk) shaped, whose True entries are a prefix of each row -- it is
-        # the per-batch number of existing keys (``fa_b200_problem.kv_lens``).  The prefix property is
-        # asserted on the device without a host synchronisation.
-        kv_lens = _key_padding_lengths(attn_mask, query, key)
+        # The reference refuses every mask (:21-24).  Here: (1) a boolean key-padding mask, (B, 1, 1, Lk)
+        # or (B, Lk) shaped, whose True entries are a prefix of each row, is the per-batch number of
+        # existing keys (``fa_b200_problem.kv_lens``: padded KV tiles are skipped; the prefix property is
+        # asserted on the device without a host synchronisation; KEY_PADDING_FAST_PATH = False sends such
+        # masks down path 2 instead, e.g. for left padding); (2) any other boolean or float mask that
+        # broadcasts to (B, H, Lq, Lk) is added to the scores inside the kernels (``fa_b200_problem.bias``).
+        # Both on the tensor path only (bf16 / fp16, D in {64, 128}); everything else keeps the error.
+        if KEY_PADDING_FAST_PATH:
+            kv_lens = _key_padding_lengths(attn_mask, query, key)
         if kv_lens is None:
+            bias = _additive_bias(attn_mask, query, key)
+        if kv_lens is None and bias is None:
             raise NotImplementedError(
-                "flash_attention_ipu supports attn_mask only as a boolean key-padding mask of shape "
-                "(B, 1, 1, Lk) whose True entries form a prefix of every row (bf16 / fp16, D in {64, 128})")
+                "flash_attention_ipu supports attn_mask only for 4-D bf16 / fp16 CUDA tensors with D in {64, 128}: "
+                "a boolean or float mask broadcastable to (B, H, Lq, Lk) with Lk % 8 == 0 and no gradient")
+        if bias is not None and dropout_p > 0.0:
+            raise NotImplementedError("flash_attention_ipu does not support attn_mask together with dropout_p > 0")
     dropout_seed = 0
     if dropout_p > 0.0:
         # The reference refuses dropout (:25-28).  Here the tcgen05 kernels apply it (16-bit, D in {64, 128});
@@ -115,7 +145,7 @@ def _sdpa_impl(
     else:
         q, k, v = (t.reshape(1, -1, L, D) for t in (query, key, value))
     out, _lse = ops.attention_fwd(q, k, v, softmax_scale, bool(is_causal),
-                                  L // num_chunks_q, L // num_chunks_kv, kv_lens, float(dropout_p), dropout_seed)
+                                  L // num_chunks_q, L // num_chunks_kv, kv_lens, float(dropout_p), dropout_seed, bias)
     return out.reshape(*batch_shape, L, D) if query.ndim != 4 else out
 
 

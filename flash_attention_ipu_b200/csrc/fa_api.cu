@@ -94,6 +94,17 @@ int check_problem(const fa_b200_problem *p) {
       return fail(FA_B200_ERR_UNSUPPORTED, "dropout needs the tensor path (16-bit, D in {64,128})");
     if (p->kv_pos0 % 4) return fail(FA_B200_ERR_INVALID, "dropout needs kv_pos0 to be a multiple of 4 (one hash word covers 4 keys)");
   }
+  if (p->bias) {
+    if (!(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
+      return fail(FA_B200_ERR_UNSUPPORTED, "an additive bias needs the tensor path (16-bit, D in {64,128})");
+    if (p->dropout_p > 0.f) return fail(FA_B200_ERR_UNSUPPORTED, "bias and dropout together are not supported");
+    if (p->Lk % 8 || reinterpret_cast<uintptr_t>(p->bias) % 16 || p->bias_stride_l % 8 || p->bias_stride_h % 8 ||
+        p->bias_stride_b % 8 || (p->bias_stride_l != 0 && p->bias_stride_l < p->Lk) || p->bias_stride_h < 0 ||
+        p->bias_stride_b < 0)
+      return fail(FA_B200_ERR_INVALID,
+                  "bias needs Lk %% 8 == 0, a 16-byte aligned pointer, strides that are multiples of 8 elements and "
+                  "a row stride that is 0 (one row for every query) or >= Lk");
+  }
   // every kernel folds (tiles x groups) into a 1-D grid
   const int64_t lmax = p->Lq > p->Lk ? p->Lq : p->Lk;
   if ((int64_t)p->B * p->H * ((lmax + 63) / 64) > INT32_MAX)
@@ -459,9 +470,13 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   fp.drop_scale = drop_scale(p);
   fp.drop_q0 = p->q_pos0;
   fp.drop_k40 = p->kv_pos0 / 4;
-  auto kern = drop ? fa::fa_fwd_sm100_kernel<D, kBf16, true> : fa::fa_fwd_sm100_kernel<D, kBf16, false>;
-  static std::atomic<uint64_t> smem_ok[2] = {{0}, {0}};  // per instantiation
-  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok[drop])) return rc;
+  const bool bias = p->bias != nullptr;
+  fp.bias = reinterpret_cast<const uint16_t *>(p->bias);
+  fp.bias_sb = p->bias_stride_b; fp.bias_sh = p->bias_stride_h; fp.bias_sl = p->bias_stride_l;
+  auto kern = bias ? fa::fa_fwd_sm100_kernel<D, kBf16, false, true>
+              : drop ? fa::fa_fwd_sm100_kernel<D, kBf16, true, false> : fa::fa_fwd_sm100_kernel<D, kBf16, false, false>;
+  static std::atomic<uint64_t> smem_ok[3] = {{0}, {0}, {0}};  // per instantiation
+  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok[bias ? 2 : drop])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory); with no more items
   // than SMs every CTA runs exactly one and no counter is needed
   const int sms = sm_count();
@@ -538,10 +553,14 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   bp.drop_scale = drop_scale(p);
   bp.drop_q0 = p->q_pos0;
   bp.drop_k40 = p->kv_pos0 / 4;
-  auto kern = drop ? (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false, true>)
-                   : (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, false> : fa::fa_bwd_sm100_kernel<D, kBf16, false, false>);
-  static std::atomic<uint64_t> smem_ok[4] = {{0}, {0}, {0}, {0}};
-  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * drop])) return rc;
+  const bool bias = p->bias != nullptr;
+  bp.bias = reinterpret_cast<const uint16_t *>(p->bias);
+  bp.bias_sb = p->bias_stride_b; bp.bias_sh = p->bias_stride_h; bp.bias_sl = p->bias_stride_l;
+  auto kern = bias   ? (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, false, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false, false, true>)
+              : drop ? (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, true, false> : fa::fa_bwd_sm100_kernel<D, kBf16, false, true, false>)
+                     : (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, false, false> : fa::fa_bwd_sm100_kernel<D, kBf16, false, false, false>);
+  static std::atomic<uint64_t> smem_ok[6] = {{0}, {0}, {0}, {0}, {0}, {0}};
+  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * (bias ? 2 : drop)])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory), items by atomic counter
   const unsigned grid = (unsigned)(items < sm_count() ? items : sm_count());
 #ifdef FA_BWD_TRACE

@@ -92,6 +92,10 @@ struct BwdParams {
   uint32_t drop_thresh4, drop_seed;
   float drop_scale;
   int drop_q0, drop_k40;
+  // additive score bias (kBias instantiation only), as in FwdParams.  It only enters P = exp(S' - LSE); dS is
+  // the gradient with respect to S' as well, so dQ / dK / dV need nothing else (no gradient for the bias itself)
+  const uint16_t *bias;
+  long long bias_sb, bias_sh, bias_sl;
 #ifdef FA_BWD_TRACE
   unsigned long long *trace;  // CTA 0: cycles the MMA warp spent in each of its waits
 #endif
@@ -173,7 +177,7 @@ __device__ __forceinline__ void bwd_next_tile(int &h, int &i, int i0, int num_q_
 // kDrop = dropout on P: with M the keep mask and s = 1 / (1 - p), the forward computed O = s (M o P) V, so
 //   dV = s (M o P)^T dO   (the thinned P^T is the A operand; s is applied once, at the item's end)
 //   dS = P o (s M o dP - delta)   with delta = rowsum(O o dO) as before and P the UNdropped softmax.
-template <int D, bool kBf16, bool kGqa, bool kDrop = false>
+template <int D, bool kBf16, bool kGqa, bool kDrop = false, bool kBias = false>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -508,6 +512,18 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int c4 = 0; c4 < 16; ++c4) {
           const float4 l4 = stat[c4];
           nl[4 * c4] = l4.x; nl[4 * c4 + 1] = l4.y; nl[4 * c4 + 2] = l4.z; nl[4 * c4 + 3] = l4.w;
+        }
+        if (kBias) {
+          // bias[q][key] * log2(e) folded into -lse2 of the query column: thread <-> key, so the 32 lanes of a
+          // warp read 32 neighbouring keys of one query row (one 64-byte segment per load)
+          const uint16_t *bcol = p.bias + t.b * p.bias_sb + (t.h0 + hx) * p.bias_sh + key;
+          const int q0 = i * 128 + 64 * wg;
+          #pragma unroll
+          for (int c = 0; c < 64; ++c) {
+            const bool ok = q0 + c < p.Lq && key < p.Lk;
+            const float bv = ok ? unpack1<kBf16>(__ldg(bcol + static_cast<long long>(q0 + c) * p.bias_sl)) : 0.f;
+            nl[c] = fmaf(bv, kLog2e, nl[c]);
+          }
         }
         // dropout: bit c of keepm = query column c of this warpgroup keeps this thread's key (generated
         // ahead of the S^T wait; sm100_ptx.cuh: drop_hash -- thread <-> key, so one hash per query)

@@ -92,6 +92,10 @@ struct FwdParams {
   uint32_t drop_seed;     // 32-bit fold of fa_b200_problem.dropout_seed
   float drop_scale;       // 256 / (256 - thresh)
   int drop_q0, drop_k40;  // q_pos0 ; kv_pos0 / 4 (global positions feed the hash)
+  // additive score bias (kBias instantiation only): S' = scale * q.k + bias[b][h][q][k], bias in the kernel's
+  // 16-bit dtype, element strides (0 = broadcast over that dim), unit stride on k
+  const uint16_t *bias;
+  long long bias_sb, bias_sh, bias_sl;
 };
 
 template <int D>
@@ -143,7 +147,7 @@ __device__ __forceinline__ FwdItem fwd_decode(const FwdParams &p, int w) {
   return t;
 }
 
-template <int D, bool kBf16, bool kDrop = false>
+template <int D, bool kBf16, bool kDrop = false, bool kBias = false>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -363,6 +367,9 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint32_t drop_qh = kDrop ? drop_seed_of_group(p.drop_seed, static_cast<uint32_t>(t.g)) ^
                                        (static_cast<uint32_t>(p.drop_q0 + row) * 0x9E3779B1u) : 0u;
 
+      const uint16_t *bias_row = kBias ? p.bias + t.b * p.bias_sb + t.h * p.bias_sh + static_cast<long long>(row) * p.bias_sl
+                                       : nullptr;
+
       float m_used = -INFINITY;  // reference max (log2 domain) the exponentials are taken against
       float l = 0.f;
       for (int j = 0; j < n; ++j, ++cs) {
@@ -373,8 +380,32 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, sr[c]);
         tmem_ld_wait();
 
-        // mask (only tiles that cross the causal diagonal or the end of the keys)
         const int col0 = j * kBlockN;
+        if (kBias) {
+          // S' = S * scale + bias, taken to the log2 domain here (the exponentials below then use sr as it is).
+          // Each thread reads its own row of the bias tile: 16-byte loads, 8 keys each (Lk % 8 == 0 is checked
+          // by the shim, so a vector is either entirely inside the row or entirely beyond it)
+          const bool row_ok = row < p.Lq;
+          #pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            #pragma unroll
+            for (int v8 = 0; v8 < 4; ++v8) {
+              const int col = col0 + c * 32 + v8 * 8;
+              uint4 bv = make_uint4(0u, 0u, 0u, 0u);
+              if (row_ok && col + 8 <= p.Lk) bv = __ldg(reinterpret_cast<const uint4 *>(bias_row + col));
+              const uint32_t w4[4] = {bv.x, bv.y, bv.z, bv.w};
+              #pragma unroll
+              for (int e2 = 0; e2 < 4; ++e2) {
+                float b0, b1;
+                unpack2<kBf16>(w4[e2], b0, b1);
+                const int e = v8 * 8 + e2 * 2;
+                sr[c][e] = __float_as_uint(fmaf(__uint_as_float(sr[c][e]), p.scale_log2, b0 * kLog2e));
+                sr[c][e + 1] = __float_as_uint(fmaf(__uint_as_float(sr[c][e + 1]), p.scale_log2, b1 * kLog2e));
+              }
+            }
+          }
+        }
+        // mask (only tiles that cross the causal diagonal or the end of the keys)
         const bool tile_masked = (p.causal && col0 + kBlockN - 1 > (t.t0 + i) * kBlockM + p.shift) ||
                                  (col0 + kBlockN > t.lk);
         if (tile_masked) {
@@ -393,7 +424,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           for (int e = 0; e < 32; e += 2)
             mx4[(e >> 1) & 3] = fmax3(mx4[(e >> 1) & 3], __uint_as_float(sr[c][e]), __uint_as_float(sr[c][e + 1]));
         const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-        const float m_new = mx * p.scale_log2;
+        const float m_new = kBias ? mx : mx * p.scale_log2;  // with a bias the scores are already scaled
 
         // lazy rescale of the running accumulator
         const bool grow = m_new > m_used + kRescaleThreshold;  // also true when m_used == -inf
@@ -416,7 +447,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         // P = exp2(S * scale_log2 - m): packed FFMA2 for the argument; every kFwdPolyEvery-th pair of
         // exponentials runs as a polynomial on the FMA pipe instead of MUFU (never on masked tiles:
         // the polynomial clamps at 2^-126 instead of returning an exact 0 for -inf)
-        const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2), nm2 = f2_pack(-m_eff, -m_eff);
+        const float sc1 = kBias ? 1.f : p.scale_log2;
+        const uint64_t sc2 = f2_pack(sc1, sc1), nm2 = f2_pack(-m_eff, -m_eff);
         uint64_t sum2[4] = {0ull, 0ull, 0ull, 0ull};
         auto exp_tile = [&](auto use_poly) {
           #pragma unroll
@@ -453,7 +485,8 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             }
           }
         };
-        if (tile_masked) exp_tile(BoolC<false>{}); else exp_tile(BoolC<true>{});
+        // a bias may hold -inf anywhere: like masked tiles, never through the polynomial
+        if (tile_masked || kBias) exp_tile(BoolC<false>{}); else exp_tile(BoolC<true>{});
         {
           float a0, a1;
           f2_unpack(f2_add(f2_add(sum2[0], sum2[1]), f2_add(sum2[2], sum2[3])), a0, a1);

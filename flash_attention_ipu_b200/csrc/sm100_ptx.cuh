@@ -564,6 +564,24 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   return r;
 }
 
+// two 16-bit floats of one 32-bit word -> fp32 (lo = element 0)
+template <bool kBf16>
+__device__ __forceinline__ void unpack2(uint32_t w, float &a, float &b) {
+  if (kBf16) {
+    a = __uint_as_float(w << 16);
+    b = __uint_as_float(w & 0xffff0000u);
+  } else {
+    asm("{\n\t.reg .b16 lo, hi;\n\tmov.b32 {lo, hi}, %2;\n\tcvt.f32.f16 %0, lo;\n\tcvt.f32.f16 %1, hi;\n\t}"
+        : "=f"(a), "=f"(b) : "r"(w));
+  }
+}
+template <bool kBf16>
+__device__ __forceinline__ float unpack1(uint16_t h) {
+  float a, b;
+  unpack2<kBf16>(static_cast<uint32_t>(h), a, b);
+  return a;
+}
+
 // ---------------------------------------------------------------- programmatic dependent launch
 // A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may be scheduled before
 // the kernel ahead of it in the stream has finished: its CTAs run their prologue (barrier init, TMEM

@@ -126,6 +126,32 @@ fa_b200_problem make_problem(const Tensor &q, const Tensor &k, bool causal, doub
   return p;
 }
 
+// Additive score bias (the float form of attn_mask): (B|1, H|1, Lq, Lk) in q's dtype.  Returned in a form the
+// kernels address in place (unit stride on Lk, 16-byte aligned rows), so that the caller keeps it alive.
+Tensor bias_or_empty(const std::optional<Tensor> &bias, const Tensor &q, const Tensor &k) {
+  if (!bias.has_value() || !bias->defined()) return Tensor();
+  const Tensor &b = *bias;
+  TORCH_CHECK(b.is_cuda() && b.device() == q.device(), "bias must be on q's device");
+  TORCH_CHECK(b.scalar_type() == q.scalar_type(), "bias must have q's dtype, got ", b.scalar_type());
+  TORCH_CHECK(b.dim() == 4 && b.size(2) == q.size(2) && b.size(3) == k.size(2) && (b.size(0) == 1 || b.size(0) == q.size(0)) &&
+                  (b.size(1) == 1 || b.size(1) == q.size(1)),
+              "bias of shape ", b.sizes(), " is not (B|1, H|1, Lq, Lk) for q ", q.sizes(), " and k ", k.sizes());
+  TORCH_CHECK(!b.requires_grad(), "no gradient is produced for the attention bias");
+  // a stride of 0 (an expanded dim) is fine on every dim but the last: the kernels only multiply by it
+  bool ok = b.stride(3) == 1 && reinterpret_cast<uintptr_t>(b.data_ptr()) % 16 == 0 &&
+            (b.stride(2) == 0 || (b.stride(2) % 8 == 0 && b.stride(2) >= b.size(3)));
+  for (int64_t i = 0; ok && i < 2; ++i) ok = b.size(i) == 1 || (b.stride(i) >= 0 && b.stride(i) % 8 == 0);
+  return ok ? b : b.contiguous();
+}
+
+void set_bias(fa_b200_problem &p, const Tensor &b) {
+  if (!b.defined()) return;
+  p.bias = b.data_ptr();
+  p.bias_stride_b = b.size(0) > 1 ? b.stride(0) : 0;
+  p.bias_stride_h = b.size(1) > 1 ? b.stride(1) : 0;
+  p.bias_stride_l = b.stride(2);
+}
+
 void check(int rc, const char *what) {
   TORCH_CHECK(rc == 0, what, " failed (status ", rc, "): ", fa_b200_last_error());
 }
@@ -158,7 +184,8 @@ void run_bwd(const fa_b200_problem &p, const Tensor &q, const Tensor &k, const T
 // ------------------------------------------------------------------ separate q, k, v (SDPA path)
 std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, const Tensor &v_, double scale,
                                          bool causal, int64_t block_q, int64_t block_kv,
-                                         const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed) {
+                                         const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed,
+                                         const std::optional<Tensor> &bias_) {
   require_cuda({&q_, &k_, &v_});
   check_operands(q_, k_, v_, nullptr, nullptr, nullptr);
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_);
@@ -166,7 +193,10 @@ std::tuple<Tensor, Tensor> attention_fwd(const Tensor &q_, const Tensor &k_, con
   if (out.stride(-1) != 1) out = at::empty(q.sizes(), q.options());
   const Tensor lse = at::empty({q.size(0), q.size(1), q.size(2)}, q.options().dtype(at::kFloat));
   const Tensor lens = lens_or_empty(kv_lens, q);
-  run_fwd(make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed), q, k, v, out, lse);
+  const Tensor bias = bias_or_empty(bias_, q, k);
+  fa_b200_problem prob = make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed);
+  set_bias(prob, bias);
+  run_fwd(prob, q, k, v, out, lse);
   return {out, lse};
 }
 
@@ -174,14 +204,17 @@ std::tuple<Tensor, Tensor, Tensor> attention_bwd(const Tensor &dout_, const Tens
                                                  const Tensor &v_, const Tensor &out_, const Tensor &lse_,
                                                  double scale, bool causal, int64_t block_q, int64_t block_kv,
                                                  const std::optional<Tensor> &kv_lens, double dropout_p,
-                                                 int64_t dropout_seed) {
+                                                 int64_t dropout_seed, const std::optional<Tensor> &bias_) {
   require_cuda({&dout_, &q_, &k_, &v_, &out_, &lse_});
   check_operands(q_, k_, v_, &out_, &dout_, &lse_);
   const Tensor lse = lse_.contiguous();  // the kernels index it as a dense [B*H][Lq] array
   const Tensor q = as_bhld(q_), k = as_bhld(k_), v = as_bhld(v_), out = as_bhld(out_), dout = as_bhld(dout_);
   const Tensor dq = at::empty_like(q), dk = at::empty_like(k), dv = at::empty_like(v);
   const Tensor lens = lens_or_empty(kv_lens, q);
-  run_bwd(make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed), q, k, v, out, dout, lse, dq, dk, dv);
+  const Tensor bias = bias_or_empty(bias_, q, k);
+  fa_b200_problem prob = make_problem(q, k, causal, scale, block_q, block_kv, lens, dropout_p, dropout_seed);
+  set_bias(prob, bias);
+  run_bwd(prob, q, k, v, out, dout, lse, dq, dk, dv);
   return {dq, dk, dv};
 }
 
@@ -233,15 +266,18 @@ auto typed_op(const char *name) {
 struct AttentionFn : public torch::autograd::Function<AttentionFn> {
   static variable_list forward(AutogradContext *ctx, const Tensor &q, const Tensor &k, const Tensor &v,
                                double scale, bool causal, int64_t block_q, int64_t block_kv,
-                               const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed) {
+                               const std::optional<Tensor> &kv_lens, double dropout_p, int64_t dropout_seed,
+                               const std::optional<Tensor> &bias) {
     at::AutoDispatchBelowADInplaceOrView below;
     static auto op = typed_op<std::tuple<Tensor, Tensor>(const Tensor &, const Tensor &, const Tensor &, double,
                                                          bool, int64_t, int64_t, const std::optional<Tensor> &, double,
-                                                         int64_t)>("flash_attention_ipu::attention_fwd");
-    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed);
+                                                         int64_t, const std::optional<Tensor> &)>(
+        "flash_attention_ipu::attention_fwd");
+    auto [out, lse] = op.call(q, k, v, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed, bias);
     ctx->saved_data["dropout_p"] = dropout_p;      // the backward regenerates the forward's mask from the seed
     ctx->saved_data["dropout_seed"] = dropout_seed;
-    ctx->save_for_backward({q, k, v, out, lse, kv_lens.has_value() ? *kv_lens : Tensor()});
+    ctx->save_for_backward({q, k, v, out, lse, kv_lens.has_value() ? *kv_lens : Tensor(),
+                            bias.has_value() ? *bias : Tensor()});
     ctx->saved_data["scale"] = scale;
     ctx->saved_data["causal"] = causal;
     ctx->saved_data["block_q"] = block_q;
@@ -252,15 +288,17 @@ struct AttentionFn : public torch::autograd::Function<AttentionFn> {
   static variable_list backward(AutogradContext *ctx, variable_list grads) {
     static auto op = typed_op<std::tuple<Tensor, Tensor, Tensor>(
         const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, const Tensor &, double, bool,
-        int64_t, int64_t, const std::optional<Tensor> &, double, int64_t)>("flash_attention_ipu::attention_bwd");
+        int64_t, int64_t, const std::optional<Tensor> &, double, int64_t, const std::optional<Tensor> &)>(
+        "flash_attention_ipu::attention_bwd");
     const auto saved = ctx->get_saved_variables();
     const Tensor dout = grads[0].defined() ? grads[0] : at::zeros_like(saved[3]);
     const std::optional<Tensor> lens = saved[5].defined() ? std::optional<Tensor>(saved[5]) : std::nullopt;
+    const std::optional<Tensor> bias = saved[6].defined() ? std::optional<Tensor>(saved[6]) : std::nullopt;
     auto [dq, dk, dv] = op.call(dout, saved[0], saved[1], saved[2], saved[3], saved[4],
                                 ctx->saved_data["scale"].toDouble(), ctx->saved_data["causal"].toBool(),
                                 ctx->saved_data["block_q"].toInt(), ctx->saved_data["block_kv"].toInt(), lens,
-                                ctx->saved_data["dropout_p"].toDouble(), ctx->saved_data["dropout_seed"].toInt());
-    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
+                                ctx->saved_data["dropout_p"].toDouble(), ctx->saved_data["dropout_seed"].toInt(), bias);
+    return {dq, dk, dv, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor()};
   }
 };
 
@@ -301,8 +339,8 @@ struct PackedFn : public torch::autograd::Function<PackedFn> {
 std::tuple<Tensor, Tensor> attention_fwd_autograd(const Tensor &q, const Tensor &k, const Tensor &v, double scale,
                                                   bool causal, int64_t block_q, int64_t block_kv,
                                                   const std::optional<Tensor> &kv_lens, double dropout_p,
-                                                  int64_t dropout_seed) {
-  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed);
+                                                  int64_t dropout_seed, const std::optional<Tensor> &bias) {
+  auto r = AttentionFn::apply(q, k, v, scale, causal, block_q, block_kv, kv_lens, dropout_p, dropout_seed, bias);
   return {r[0], r[1]};
 }
 
@@ -320,11 +358,14 @@ TORCH_LIBRARY(flash_attention_ipu, m) {
   // keys of group g exist.  The reference refuses every attn_mask (_impl/scaled_dot_product_attention.py:21-24).
   // dropout_p / dropout_seed: dropout on the attention probabilities inside the tcgen05 kernels (the reference
   // refuses dropout_p > 0, :25-28); the mask is a function of the seed, so the backward op takes the same pair.
+  // bias (attention_fwd / attention_bwd): additive score bias (B|1, H|1, Lq, Lk) in q's dtype, the float form of
+  // attn_mask; no gradient is produced for it.
   m.def("attention_fwd(Tensor q, Tensor k, Tensor v, float softmax_scale, bool causal, int block_q, "
-        "int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> (Tensor, Tensor)");
+        "int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0, Tensor? bias=None) -> "
+        "(Tensor, Tensor)");
   m.def("attention_bwd(Tensor dout, Tensor q, Tensor k, Tensor v, Tensor out, Tensor lse, float softmax_scale, "
-        "bool causal, int block_q, int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> "
-        "(Tensor, Tensor, Tensor)");
+        "bool causal, int block_q, int block_kv, Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0, "
+        "Tensor? bias=None) -> (Tensor, Tensor, Tensor)");
   m.def("qkv_packed_fwd(Tensor qkv, float softmax_scale, bool causal, int block_q, int block_kv, "
         "Tensor? kv_lens=None, float dropout_p=0.0, int dropout_seed=0) -> (Tensor, Tensor)");
   m.def("qkv_packed_bwd(Tensor dout, Tensor qkv, Tensor out, Tensor lse, float softmax_scale, bool causal, "

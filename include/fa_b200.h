@@ -72,6 +72,14 @@ typedef struct {
   uint64_t dropout_seed; /* the mask is a pure function of (dropout_seed, b*H+h, q_pos0 + row,           */
                          /* kv_pos0 + key) -- csrc/sm100_ptx.cuh: drop_hash -- so the backward must be   */
                          /* given the forward's seed; restated by oracle/attention_oracle.py.            */
+  const void *bias;      /* NULL, or a DEVICE tensor added to the scaled scores before the softmax (the   */
+                         /* additive form of attn_mask, which the reference refuses:                      */
+                         /* _impl/scaled_dot_product_attention.py:21-24): S' = scale*q.k + bias[b][h][q][k], */
+                         /* elements of `dtype`, -inf = masked.  Element strides below; 0 broadcasts the   */
+                         /* batch / head / query dim; the key dim has unit stride.  Tensor path only; Lk % 8 == 0, */
+                         /* 16-byte aligned pointer and row stride; not together with dropout; no gradient */
+                         /* is produced for the bias.                                                      */
+  int64_t bias_stride_b, bias_stride_h, bias_stride_l;
 } fa_b200_problem;
 
 /* Forward: replaces flashAttentionQKVPackedWithStash

@@ -701,7 +701,7 @@ def _masked_reference(q, k, v, dout, lens, causal, scale):
 def test_key_padding_mask_via_sdpa(B, H, L, D, causal, lens):
     """attn_mask as a boolean key-padding mask (the reference refuses every mask,
     _impl/scaled_dot_product_attention.py:21-24): out and all gradients vs fp64 math; padded keys get
-    dk = dv = 0; a mask that is not a prefix is refused."""
+    dk = dv = 0.  (Other mask forms: test_attn_mask_through_sdpa_override.)"""
     import torch.nn.functional as F
     import flash_attention_ipu_b200._impl.scaled_dot_product_attention as mod
     native = _native_loaded()
@@ -718,8 +718,8 @@ def test_key_padding_mask_via_sdpa(B, H, L, D, causal, lens):
         out.backward(dout.cuda())
         torch.cuda.synchronize()
         assert native.launch_count() > before
-        with pytest.raises(NotImplementedError, match="attn_mask"):   # additive masks stay refused
-            F.scaled_dot_product_attention(qd, kd, vd, attn_mask=torch.zeros(L, L, device="cuda", dtype=torch.bfloat16))
+        with pytest.raises(NotImplementedError, match="attn_mask"):   # a mask that does not broadcast to (B, H, Lq, Lk)
+            F.scaled_dot_product_attention(qd, kd, vd, attn_mask=torch.zeros(L, L // 2, device="cuda", dtype=torch.bfloat16))
     finally:
         mod.uninstall()
     # causal rows whose visible keys are all real: every row has at least key 0 (lens >= 1)
@@ -877,3 +877,118 @@ def test_dropout_through_sdpa_override_and_packed_api():
     with pytest.raises(NotImplementedError, match="dropout_p"):
         mod._sdpa_impl(None, torch.randn(1, 2, 64, 32, device="cuda"), torch.randn(1, 2, 64, 32, device="cuda"),
                        torch.randn(1, 2, 64, 32, device="cuda"), None, 0.1, True)
+
+
+def _bias_reference(q, k, v, dout, bias, causal, scale):
+    """fp64 attention with an additive score bias (-inf = masked); k, v may have fewer heads."""
+    q, k, v = (t.double().requires_grad_(True) for t in (q, k, v))
+    rep = q.shape[1] // k.shape[1]
+    kk, vv = k.repeat_interleave(rep, dim=1), v.repeat_interleave(rep, dim=1)
+    s = torch.einsum("bhqd,bhkd->bhqk", q, kk) * scale + bias.double()
+    if causal:
+        r = torch.arange(q.shape[2])[:, None]
+        c = torch.arange(k.shape[2])[None, :]
+        s = s.masked_fill(c > r, float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)
+    out = torch.einsum("bhqk,bhkd->bhqd", torch.exp(s - lse[..., None]), vv)
+    out.backward(dout.double())
+    return out.detach(), lse.detach(), q.grad, k.grad, v.grad
+
+
+@pytest.mark.parametrize("B,H,Hkv,Lq,Lk,D,causal,dtype,bshape", [
+    (2, 2, 2, 200, 328, 128, False, "bf16", "full"),    # ragged lengths, one bias row per (b, h, q)
+    (1, 3, 3, 384, 384, 64, True, "fp16", "head"),      # (1, H, Lq, Lk): broadcast over the batch, with the causal mask
+    (2, 4, 2, 256, 256, 128, False, "bf16", "keys"),    # grouped-query; (B, 1, 1, Lk): one row for every query (stride 0)
+])
+def test_additive_bias_through_the_c_abi(B, H, Hkv, Lq, Lk, D, causal, dtype, bshape):
+    """fa_b200_problem.bias: S' = scale q.k + bias with -inf entries, forward and backward of both tcgen05
+    kernels against fp64 math on the same (rounded) bias."""
+    native = _native_loaded()
+    torch.manual_seed(SEED + Lq + D)
+    dt = DT[dtype]
+    q, dout = (torch.randn(B, H, Lq, D).to(dt) for _ in range(2))
+    k, v = (torch.randn(B, Hkv, Lk, D).to(dt) for _ in range(2))
+    shape = {"full": (B, H, Lq, Lk), "head": (1, H, Lq, Lk), "keys": (B, 1, 1, Lk)}[bshape]
+    bias = (2.0 * torch.randn(shape)).to(dt)
+    hole = torch.rand(shape) < 0.3
+    hole[..., 0] = False                                 # every row keeps key 0 (also under the causal mask)
+    bias = bias.masked_fill(hole, float("-inf"))
+    scale = D ** -0.5
+    ref = _bias_reference(q.float(), k.float(), v.float(), dout.float(), bias.float().expand(B, H, Lq, Lk), causal, scale)
+    qd, kd, vd, dd = (t.cuda() for t in (q, k, v, dout))
+    bd = bias.cuda().expand(shape[0], shape[1], Lq, Lk)
+    prob = native.make_problem(qd, kd, causal, scale, bias=bd)
+    assert native.kernel_family(prob) == 1
+    o = torch.empty_like(qd)
+    lse = torch.empty(B, H, Lq, device="cuda", dtype=torch.float32)
+    native.fwd(prob, qd, kd, vd, o, lse)
+    dq, dk, dv = torch.empty_like(qd), torch.empty_like(kd), torch.empty_like(vd)
+    ws = torch.empty(native.bwd_workspace_bytes(prob), device="cuda", dtype=torch.uint8)
+    native.bwd(prob, qd, kd, vd, o, dd, lse, dq, dk, dv, ws)
+    torch.cuda.synchronize()
+    assert (lse.cpu().double() - ref[1]).abs().max().item() <= 1e-2
+    assert (o.cpu().double() - ref[0]).abs().max().item() <= 2e-2
+    assert rel_fro(o.cpu().double(), ref[0]) < 1e-2
+    for got, want in zip((dq, dk, dv), (ref[2], ref[3], ref[4])):
+        assert rel_fro(got.cpu().double(), want) < 1e-2
+    # refused: Lk not a multiple of 8, bias together with dropout, bias off the tensor path
+    with pytest.raises(RuntimeError, match="bias"):
+        bad = native.make_problem(qd, kd, causal, scale, bias=bd, dropout_p=0.1)
+        native.fwd(bad, qd, kd, vd, o, lse)
+    k7 = kd[:, :, :Lk - 1].contiguous()
+    with pytest.raises(RuntimeError, match="bias"):
+        bad = native.make_problem(qd, k7, causal, scale, bias=torch.zeros(B, H, Lq, Lk - 1, device="cuda", dtype=dt))
+        native.fwd(bad, qd, k7, k7, o, lse)
+
+
+def test_attn_mask_through_sdpa_override():
+    """Float and boolean attn_mask (not of the key-padding form) through F.scaled_dot_product_attention: routed to
+    the kernels (launch counter) and equal to torch's own masked SDPA run in fp32 on the CPU."""
+    import torch.nn.functional as F
+    import flash_attention_ipu_b200._impl.scaled_dot_product_attention as mod
+    native = _native_loaded()
+    torch.manual_seed(SEED)
+    B, H, L, D = 2, 4, 256, 64
+    q, k, v, dout = (torch.randn(B, H, L, D).bfloat16() for _ in range(4))
+    idx = torch.arange(L)
+    band = (idx[:, None] - idx[None, :]).abs() <= 96                      # (L, L) boolean sliding window
+    alibi = -0.05 * (idx[:, None] - idx[None, :]).abs().float()           # float, one slope per head below
+    masks = {
+        "bool_2d": band,
+        "bool_4d": band[None, None] & (torch.rand(B, 1, L, L) < 0.9) | torch.eye(L, dtype=torch.bool),
+        "float_heads": (alibi[None, None] * torch.tensor([1.0, 2.0, 4.0, 8.0])[None, :, None, None]).bfloat16(),
+    }
+    orig = F.scaled_dot_product_attention.__wrapped__ if hasattr(F.scaled_dot_product_attention, "__wrapped__") \
+        else F.scaled_dot_product_attention
+    mod.install()
+    try:
+        for name, mask in masks.items():
+            xs = [t.float().requires_grad_(True) for t in (q, k, v)]
+            mref = mask if mask.dtype == torch.bool else mask.float()
+            ref = orig(*xs, attn_mask=mref)
+            ref.backward(dout.float())
+            ys = [t.cuda().requires_grad_(True) for t in (q, k, v)]
+            before = native.launch_count()
+            out = F.scaled_dot_product_attention(*ys, attn_mask=mask.cuda())
+            out.backward(dout.cuda())
+            torch.cuda.synchronize()
+            assert native.launch_count() - before >= 3, name
+            assert (out.detach().float().cpu() - ref.detach()).abs().max().item() <= 2e-2, name
+            for got, want in zip(ys, xs):
+                assert rel_fro(got.grad.float().cpu(), want.grad) < 1e-2, name
+        # key-padding shaped boolean masks with holes (left padding): the fast path off -> additive path
+        mod.KEY_PADDING_FAST_PATH = False
+        left = torch.ones(B, 1, 1, L, dtype=torch.bool)
+        left[0, ..., :40] = False
+        ys = [t.cuda() for t in (q, k, v)]
+        out = F.scaled_dot_product_attention(*ys, attn_mask=left.cuda())
+        ref = orig(q.float(), k.float(), v.float(), attn_mask=left)
+        assert (out.float().cpu() - ref).abs().max().item() <= 2e-2
+        # a mask that wants a gradient, or together with dropout, keeps the reference's refusal
+        with pytest.raises(NotImplementedError):
+            F.scaled_dot_product_attention(*ys, attn_mask=torch.zeros(L, L, device="cuda", dtype=torch.bfloat16, requires_grad=True))
+        with pytest.raises(NotImplementedError, match="dropout"):
+            F.scaled_dot_product_attention(*ys, attn_mask=band.cuda(), dropout_p=0.1)
+    finally:
+        mod.KEY_PADDING_FAST_PATH = True
+        mod.uninstall()
