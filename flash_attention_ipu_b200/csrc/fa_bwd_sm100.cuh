@@ -518,11 +518,26 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           // warp read 32 neighbouring keys of one query row (one 64-byte segment per load)
           const uint16_t *bcol = p.bias + t.b * p.bias_sb + (t.h0 + hx) * p.bias_sh + key;
           const int q0 = i * 128 + 64 * wg;
+          // two batches of 32 independent loads (all issued before the first is used), each under the wait for S^T
           #pragma unroll
-          for (int c = 0; c < 64; ++c) {
-            const bool ok = q0 + c < p.Lq && key < p.Lk;
-            const float bv = ok ? unpack1<kBf16>(__ldg(bcol + static_cast<long long>(q0 + c) * p.bias_sl)) : 0.f;
-            nl[c] = fmaf(bv, kLog2e, nl[c]);
+          for (int c0 = 0; c0 < 64; c0 += 32) {
+            uint16_t raw[32];
+            #pragma unroll
+            for (int c = 0; c < 32; ++c) {
+              const bool ok = q0 + c0 + c < p.Lq && key < p.Lk;
+              raw[c] = ok ? __ldg(bcol + static_cast<long long>(q0 + c0 + c) * p.bias_sl) : static_cast<uint16_t>(0);
+            }
+            #pragma unroll
+            for (int c = 0; c < 32; ++c) nl[c0 + c] = fmaf(unpack1<kBf16>(raw[c]), kLog2e, nl[c0 + c]);
+          }
+          // the next Q tile's 64 rows of this warp's keys -> L2 (two rows per lane)
+          if (i + 1 < num_q_tiles) {
+            #pragma unroll
+            for (int r2 = 0; r2 < 2; ++r2) {
+              const int qn = (i + 1) * 128 + 64 * wg + 2 * lane + r2;
+              if (qn < p.Lq && key < p.Lk)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(bcol - lane + static_cast<long long>(qn) * p.bias_sl));
+            }
           }
         }
         // dropout: bit c of keepm = query column c of this warpgroup keeps this thread's key (generated

@@ -373,6 +373,26 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       float m_used = -INFINITY;  // reference max (log2 domain) the exponentials are taken against
       float l = 0.f;
       for (int j = 0; j < n; ++j, ++cs) {
+        // bias of this thread's row of the tile: 16 independent 16-byte loads (8 keys each), issued BEFORE the
+        // wait for S so that their latency runs under it (Lk % 8 == 0 is checked by the shim, so a vector is
+        // either entirely inside the row or entirely beyond it); the next tile's two lines are pulled into L2
+        uint4 bv[kBias ? 16 : 1];
+        if (kBias) {
+          const bool row_ok = row < p.Lq;
+          #pragma unroll
+          for (int v = 0; v < 16; ++v) {
+            const int col = j * kBlockN + v * 8;
+            bv[v] = make_uint4(0u, 0u, 0u, 0u);
+            if (row_ok && col + 8 <= p.Lk) bv[v] = __ldg(reinterpret_cast<const uint4 *>(bias_row + col));
+          }
+          if (row_ok && j + 1 < n) {
+            #pragma unroll
+            for (int ln = 0; ln < 2; ++ln) {
+              const int col = (j + 1) * kBlockN + ln * 64;
+              if (col < p.Lk) asm volatile("prefetch.global.L2 [%0];" ::"l"(bias_row + col));
+            }
+          }
+        }
         mbar_wait(&s_full[i], cs & 1);
         tc_fence_after();
         uint32_t sr[4][32];
@@ -382,18 +402,13 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
         const int col0 = j * kBlockN;
         if (kBias) {
-          // S' = S * scale + bias, taken to the log2 domain here (the exponentials below then use sr as it is).
-          // Each thread reads its own row of the bias tile: 16-byte loads, 8 keys each (Lk % 8 == 0 is checked
-          // by the shim, so a vector is either entirely inside the row or entirely beyond it)
-          const bool row_ok = row < p.Lq;
+          // S' = S * scale + bias, taken to the log2 domain here (the exponentials below then use sr as it is)
           #pragma unroll
           for (int c = 0; c < 4; ++c) {
             #pragma unroll
             for (int v8 = 0; v8 < 4; ++v8) {
-              const int col = col0 + c * 32 + v8 * 8;
-              uint4 bv = make_uint4(0u, 0u, 0u, 0u);
-              if (row_ok && col + 8 <= p.Lk) bv = __ldg(reinterpret_cast<const uint4 *>(bias_row + col));
-              const uint32_t w4[4] = {bv.x, bv.y, bv.z, bv.w};
+              const uint4 b4 = bv[c * 4 + v8];
+              const uint32_t w4[4] = {b4.x, b4.y, b4.z, b4.w};
               #pragma unroll
               for (int e2 = 0; e2 < 4; ++e2) {
                 float b0, b1;
