@@ -50,6 +50,14 @@ constexpr int kFwdThreads = 384;
 #ifndef FA_FWD_K_STAGES
 #define FA_FWD_K_STAGES 3
 #endif
+#ifndef FA_FWD_OWN_OSTAGE
+#define FA_FWD_OWN_OSTAGE 1
+#endif
+// D = 64 leaves 80 KB of shared memory unused: the output tiles get a staging buffer of their own there, so
+// that the next item's Q tiles load as soon as this item's last S products have completed instead of after
+// its output has left (short items -- BERT / GPT-2 shapes walk 2-8 KV tiles -- pay that wait once per
+// item).  At D = 128 there is no room, and a buffer taken from the K ring measured slower (header).
+template <int D> struct FwdOwnOStage { static constexpr bool value = D == 64 && FA_FWD_OWN_OSTAGE; };
 constexpr int kKStages = FA_FWD_K_STAGES;  // K ring depth (2 measures the same once the kernel is persistent)
 #ifndef FA_FWD_V_STAGES
 #define FA_FWD_V_STAGES 2
@@ -105,7 +113,8 @@ struct FwdSmem {
   static constexpr int kQOff = 0;
   static constexpr int kKOff = kQOff + 2 * kTileBytes;
   static constexpr int kVOff = kKOff + kKStages * kTileBytes;
-  static constexpr int kBarOff = kVOff + kVStages * kTileBytes;
+  static constexpr int kOOff = kVOff + kVStages * kTileBytes;  // 2 output staging tiles (FwdOwnOStage only)
+  static constexpr int kBarOff = kOOff + (FwdOwnOStage<D>::value ? 2 * kTileBytes : 0);
   static constexpr int kNumBars = 4 + 2 * kKStages + 2 * kVStages + 2 + 2 * kPSplit + 2 + 4;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kSchedOff = kTmemPtrOff + 8;   // int[2]: scheduled item per slot (-1 = no more work)
@@ -320,6 +329,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (j < n0 && leader) {
           issue_s(0, kj);
           if (!(j < n1)) umma_commit(&k_empty[kj % kKStages]);
+          if (FwdOwnOStage<D>::value && j == n0 - 1) umma_commit(&q_empty[0]);  // Q_0 has been read for the last time
         }
         if (j >= 1 && j - 1 < n1) {
           mbar_wait(&v_full[(kj - 1) % kVStages], ((kj - 1) / kVStages) & 1);
@@ -332,6 +342,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (j < n1 && leader) {
           issue_s(1, kj);
           umma_commit(&k_empty[kj % kKStages]);
+          if (FwdOwnOStage<D>::value && j == n1 - 1) umma_commit(&q_empty[1]);
         }
         if (j < n0) {
           mbar_wait(&v_full[kj % kVStages], (kj / kVStages) & 1);
@@ -519,9 +530,15 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         ++co;
       }
       if (t.n_max > 0) {
-        uint8_t *o_smem = smem + L::kQOff + i * L::kTileBytes;  // Q_i is dead once o_full fires
+        constexpr bool kOwn = FwdOwnOStage<D>::value;
+        // staged in the dead Q_i buffer (Q_i is dead once o_full fires), or in a buffer of its own
+        uint8_t *o_smem = kOwn ? smem + L::kOOff + i * L::kTileBytes : smem + L::kQOff + i * L::kTileBytes;
         if (n == 0) mbar_wait(&q_full[i], kq & 1);              // its load must have landed before the buffer is reused
         ++kq;
+        if (kOwn) {  // the previous item's store must have read the staging buffer (long done by now)
+          if ((warp & 3) == 0 && lane == 0) tma_store_wait_read<0>();
+          named_bar_sync(1 + i, 128);
+        }
         #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
           uint32_t o[32];
@@ -551,9 +568,11 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             for (int hh = 0; hh < kHalves; ++hh)
               tma_store_4d_h<FA_FWD_HINT_OUT>(&tmO, o_smem + hh * L::kHalfBytes, hh * 64, (t.t0 + i) * kBlockM, t.h, t.b);
             tma_store_commit();
-            tma_store_wait_read<0>();
+            if (!kOwn) tma_store_wait_read<0>();
           }
-          mbar_arrive(&q_empty[i]);  // the next item's Q_i may be loaded
+          // the next item's Q_i may be loaded (own staging: the MMA warp says so after the last S_i product,
+          // unless this tile had none)
+          if (!kOwn || n == 0) mbar_arrive(&q_empty[i]);
         }
       }
       if (row < p.Lq)
@@ -562,6 +581,7 @@ fa_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       // issued after the loads above in program order
       tc_fence_before();
     }
+    if (FwdOwnOStage<D>::value && (warp & 3) == 0 && lane == 0) tma_store_wait_read<0>();  // before the CTA gives up its smem
   } else {
     reg_dealloc<88>();
   }
