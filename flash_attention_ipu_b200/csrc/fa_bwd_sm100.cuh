@@ -101,20 +101,30 @@ struct BwdParams {
 #endif
 };
 
+#ifndef FA_BWD_KV_STAGES2
+#define FA_BWD_KV_STAGES2 1
+#endif
+// D = 64 leaves 80 KB of shared memory unused: K / V get a second stage there, so that the next item's K / V
+// load while this item still runs instead of after its last MMAs (short items -- 4-8 Q tiles at the BERT /
+// GPT-2 shapes -- pay that latency once per item).  No room at D = 128, and nothing to gain with 64-tile items.
+template <int D> struct BwdKvStages { static constexpr int value = (D == 64 && FA_BWD_KV_STAGES2) ? 2 : 1; };
+
 template <int D>
 struct BwdSmem {
   static constexpr int kTileBytes = 128 * D * 2;
   static constexpr int kHalfBytes = 128 * 128;
+  static constexpr int kKvStages = BwdKvStages<D>::value;
+  static constexpr int kKvStageBytes = 2 * kTileBytes;        // K | V of one stage
   static constexpr int kKOff = 0;
   static constexpr int kVOff = kKOff + kTileBytes;
-  static constexpr int kQOff = kVOff + kTileBytes;            // 2 stages
+  static constexpr int kQOff = kKOff + kKvStages * kKvStageBytes;  // 2 stages
   static constexpr int kDOOff = kQOff + 2 * kTileBytes;       // 1 stage
   static constexpr int kDSOff = kDOOff + kTileBytes;          // dS^T [128 keys][128 q] 16-bit (item end: dK / dV staging)
   static constexpr int kDQOff = kDSOff + 2 * kHalfBytes;      // fp32 staging: 4 drain warps x 2 slabs x 4 KB
   static constexpr int kSlabBytes = 4096, kDrainSlabs = 2;
   static constexpr int kStatOff = kDQOff + 4 * kDrainSlabs * kSlabBytes;  // 2 stages x (lse2[128] | delta[128]) fp32
   static constexpr int kBarOff = kStatOff + 2 * 1024;
-  static constexpr int kNumBars = 20;
+  static constexpr int kNumBars = 22;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kSchedOff = kTmemPtrOff + 8;           // int[2]: scheduled item per slot (-1 = no more work)
   static constexpr int kBytes = kSchedOff + 8;
@@ -202,6 +212,9 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint64_t *dkv_full = bars + 13; // MMA -> compute, producer : the item's MMAs are complete (dK, dV final; K, V free)
   uint64_t *sched_full = bars + 14;   // [2] producer -> consumers : slot holds the next item
   uint64_t *sched_empty = bars + 16;  // [2] consumers -> producer : every consumer warp has read it
+  // second K / V stage (BwdKvStages): its own "full" barrier, and one "free" barrier per stage (MMA -> producer)
+  auto kv_full_of = [&](uint32_t st) -> uint64_t * { return st ? bars + 18 : kv_full; };
+  auto kv_free_of = [&](uint32_t st) -> uint64_t * { return bars + 19 + st; };
   uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(smem + L::kTmemPtrOff);
   volatile int *sched_item = reinterpret_cast<volatile int *>(smem + L::kSchedOff);
 
@@ -222,6 +235,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   if (warp == 13 && lane == 0) {
     mbar_init(kv_full, 1);
+    mbar_init(bars + 18, 1); mbar_init(bars + 19, 1); mbar_init(bars + 20, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1);
       mbar_init(&sched_full[s], 1); mbar_init(&sched_empty[s], kBwdConsumerWarps);
@@ -292,11 +306,15 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           if (it == 0) {
             // K, V after the first Q / dO tiles: those only need a free ring stage, K / V need the
             // previous item's last MMAs to have completed
-            if (kc > 0) mbar_wait(dkv_full, (kc - 1) & 1);
-            mbar_arrive_expect_tx(kv_full, 2 * L::kTileBytes);
+            const uint32_t ks = L::kKvStages == 2 ? (kc & 1) : 0;
+            if (L::kKvStages == 2) mbar_wait(kv_free_of(ks), ((kc >> 1) & 1) ^ 1);  // the item two back has left the stage
+            else if (kc > 0) mbar_wait(dkv_full, (kc - 1) & 1);
+            uint64_t *full = kv_full_of(ks);
+            uint8_t *kv_smem = smem + ks * L::kKvStageBytes;
+            mbar_arrive_expect_tx(full, 2 * L::kTileBytes);
             for (int hh = 0; hh < kHalves; ++hh) {
-              tma_load_4d_h<FA_BWD_HINT_KV>(&tmK, kv_full, smem + L::kKOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
-              tma_load_4d_h<FA_BWD_HINT_KV>(&tmV, kv_full, smem + L::kVOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
+              tma_load_4d_h<FA_BWD_HINT_KV>(&tmK, full, kv_smem + L::kKOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
+              tma_load_4d_h<FA_BWD_HINT_KV>(&tmV, full, kv_smem + L::kVOff + hh * L::kHalfBytes, hh * 64, t.j * 128, t.hk, t.b);
             }
           }
         }
@@ -316,11 +334,11 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     constexpr uint32_t hi = smem_desc_hi(1024);
     constexpr uint32_t kTile16 = L::kTileBytes >> 4;
     // K-major views (LBO unused) and MN-major views (LBO = distance between 64-column slabs)
-    const uint32_t k_kmaj = smem_desc_lo(smem_u32(smem + L::kKOff), 16);
-    const uint32_t v_kmaj = smem_desc_lo(smem_u32(smem + L::kVOff), 16);
+    const uint32_t k_kmaj0 = smem_desc_lo(smem_u32(smem + L::kKOff), 16);
+    const uint32_t v_kmaj0 = smem_desc_lo(smem_u32(smem + L::kVOff), 16);
     const uint32_t q_kmaj = smem_desc_lo(smem_u32(smem + L::kQOff), 16);
     const uint32_t do_kmaj = smem_desc_lo(smem_u32(smem + L::kDOOff), 16);
-    const uint32_t k_mn = smem_desc_lo(smem_u32(smem + L::kKOff), L::kHalfBytes);
+    const uint32_t k_mn0 = smem_desc_lo(smem_u32(smem + L::kKOff), L::kHalfBytes);
     const uint32_t q_mn = smem_desc_lo(smem_u32(smem + L::kQOff), L::kHalfBytes);
     const uint32_t do_mn = smem_desc_lo(smem_u32(smem + L::kDOOff), L::kHalfBytes);
     const uint32_t ds_mn = smem_desc_lo(smem_u32(smem + L::kDSOff), L::kHalfBytes);
@@ -349,7 +367,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (w < 0) break;
       const BwdItem t = bwd_decode<kGqa>(p, w, num_q_tiles);
       if (t.n == 0) continue;
-      mbar_wait(kv_full, kc & 1);
+      const uint32_t ks = L::kKvStages == 2 ? (kc & 1) : 0;
+      const uint32_t kv_off = ks * (L::kKvStageBytes >> 4);  // descriptor units of 16 bytes
+      const uint32_t k_kmaj = k_kmaj0 + kv_off, v_kmaj = v_kmaj0 + kv_off, k_mn = k_mn0 + kv_off;
+      mbar_wait(kv_full_of(ks), L::kKvStages == 2 ? (kc >> 1) & 1 : kc & 1);
       mbar_wait(&q_full[git & 1], (git >> 1) & 1);
       tc_fence_after();
       if (leader) {
@@ -403,7 +424,10 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         __syncwarp();
       }
-      if (leader) umma_commit(dkv_full);
+      if (leader) {
+        umma_commit(dkv_full);
+        if (L::kKvStages == 2) umma_commit(kv_free_of(ks));
+      }
       ++kc;
 #ifdef FA_BWD_TRACE
       t_last = clock64();
