@@ -992,3 +992,26 @@ def test_attn_mask_through_sdpa_override():
     finally:
         mod.KEY_PADDING_FAST_PATH = True
         mod.uninstall()
+
+
+def test_item_order_chunks_do_not_change_a_group():
+    """The persistent kernels walk the groups in L2-sized chunks (heaviest items of a chunk first; csrc/fa_api.cu:
+    order_chunk).  40 groups of T=2048, d=128 are two chunks, the second one short: every group must come out
+    exactly as when it is run alone (one chunk of one group) -- out, dK, dV bit-identical, dQ up to the
+    arrival order of its fp32 partial sums."""
+    import flash_attention_ipu as fa
+    torch.manual_seed(SEED)
+    G, L, D = 40, 2048, 128
+    qkv = torch.randn(3, G, L, D, device="cuda", dtype=torch.bfloat16)
+    qkv[0] *= D ** -0.5
+    g_out = torch.randn(G, L, D, device="cuda", dtype=torch.bfloat16)
+    x = qkv.clone().requires_grad_(True)
+    out = fa.flash_attention_qkv_packed(x, 1, 1)
+    out.backward(g_out)
+    for n in (0, 7, 31, 32, 39):
+        x1 = qkv[:, n:n + 1].clone().requires_grad_(True)
+        o1 = fa.flash_attention_qkv_packed(x1, 1, 1)
+        o1.backward(g_out[n:n + 1])
+        assert torch.equal(o1[0], out[n]), n
+        assert torch.equal(x1.grad[1, 0], x.grad[1, n]) and torch.equal(x1.grad[2, 0], x.grad[2, n]), n
+        assert rel_fro(x1.grad[0, 0].float(), x.grad[0, n].float()) < 1e-3, n
