@@ -324,6 +324,13 @@ def test_host_streamed_attention_matches_device_path():
     for _ in range(2):  # second run re-uses the staging buffers
         pipe.run(h_qkv, h_do, h_out, h_dqkv)
     torch.cuda.synchronize()
+    # the ramped schedule (1, 1, 2 | 4 | 2, 1, 1 groups: shorter fill and drain) gives the same bytes
+    h_out2, h_dqkv2 = torch.empty_like(h_out).pin_memory(), torch.empty_like(h_dqkv).pin_memory()
+    ramped = HostStreamedAttention(G, L, D, groups_per_chunk=4, ramp=True)
+    assert [n for _, n in ramped.chunks] == [1, 1, 2, 4, 2, 1, 1]
+    ramped.run(h_qkv, h_do, h_out2, h_dqkv2)
+    assert torch.equal(h_out2, h_out) and torch.equal(h_dqkv2[1:], h_dqkv[1:])
+    assert (h_dqkv2[0].float() - h_dqkv[0].float()).abs().max().item() <= 2e-2
     x = h_qkv.cuda().requires_grad_(True)
     out = fa.flash_attention_qkv_packed(x, 1, 1)
     out.backward(h_do.cuda())
