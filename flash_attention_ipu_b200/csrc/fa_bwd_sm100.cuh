@@ -565,20 +565,26 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
         }
         // dropout: bit c of keepm = query column c of this warpgroup keeps this thread's key (generated
-        // ahead of the S^T wait; sm100_ptx.cuh: drop_hash -- thread <-> key, so one hash per query)
+        // ahead of the S^T wait; sm100_ptx.cuh: drop_hash).  Thread <-> key, and one hash word covers the 4
+        // keys of 4 neighbouring lanes for one query: each of the 4 lanes computes the words of a quarter of
+        // the 64 query columns and the quad exchanges them by shuffle (a quarter of the mixing work).
         uint32_t keepm[2] = {0xffffffffu, 0xffffffffu};
         if (kDrop) {
           const uint32_t kh = drop_seed_of_group(p.drop_seed, static_cast<uint32_t>(t.b * p.H + t.h0 + hx)) ^
-                              (static_cast<uint32_t>(p.drop_k40 + (key >> 2)) * 0x85EBCA77u);
-          const uint32_t sh = (key & 3) * 8, th = p.drop_thresh4 & 0xffu;
+                              (static_cast<uint32_t>(p.drop_k40 + (key >> 2)) * 0x85EBCA77u);  // same in the 4 lanes of a quad
+          const uint32_t bit = (key & 3) * 8;  // this key's byte of the word: bit 0 of the byte after the compare
           const uint32_t q0 = static_cast<uint32_t>(p.drop_q0 + i * 128 + 64 * wg);
+          const int quad = lane & ~3, me = lane & 3;
           #pragma unroll
           for (int hf = 0; hf < 2; ++hf) {
             uint32_t m = 0;
             #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-              const uint32_t byte = (drop_mix(kh ^ ((q0 + hf * 32 + c) * 0x9E3779B1u)) >> sh) & 0xffu;
-              m |= (byte >= th ? 1u : 0u) << c;
+            for (int c4 = 0; c4 < 8; ++c4) {
+              // lane `me` of the quad: per-byte keep masks (0xff / 0x00) of query column 4 * c4 + me
+              const uint32_t mine = drop_keep_bytes(drop_mix(kh ^ ((q0 + hf * 32 + 4 * c4 + me) * 0x9E3779B1u)), p.drop_thresh4);
+              #pragma unroll
+              for (int rr = 0; rr < 4; ++rr)
+                m |= ((__shfl_sync(0xffffffffu, mine, quad | rr) >> bit) & 1u) << (4 * c4 + rr);
             }
             keepm[hf] = m;
           }
