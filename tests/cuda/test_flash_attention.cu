@@ -229,6 +229,60 @@ TEST_CASE("tensor-path tile shapes through the C ABI", "[attention][attentionGra
   }
 }
 
+// not in the reference: fa_b200_bwd_noalloc (static device scratch) against fa_b200_bwd (caller's workspace) on the
+// same inputs, twice in a row -- dK / dV bit-identical, dQ up to the arrival order of its fp32 partial sums; a
+// problem beyond the scratch is refused
+static bool run_noalloc_case(int G, int L, int D, int dtype) {
+  const size_t GLD = (size_t)G * L * D, es = 2;
+  Rng rng(4321 + L + D);
+  std::vector<float> qkv(3 * GLD), grad(GLD);
+  const float qs = 1.0f / std::sqrt((float)D);
+  for (size_t i = 0; i < 3 * GLD; ++i) qkv[i] = round_to(rng.normal() * (i < GLD ? qs : 1.f), dtype);
+  for (size_t i = 0; i < GLD; ++i) grad[i] = round_to(rng.normal(), dtype);
+  void *d_qkv, *d_o, *d_do, *d_a, *d_b, *d_ws; float *d_lse;
+  CK(cudaMalloc(&d_qkv, 3 * GLD * es)); CK(cudaMalloc(&d_o, GLD * es)); CK(cudaMalloc(&d_do, GLD * es));
+  CK(cudaMalloc(&d_a, 3 * GLD * es)); CK(cudaMalloc(&d_b, 3 * GLD * es)); CK(cudaMalloc(&d_lse, (size_t)G * L * 4));
+  to_device(qkv, dtype, d_qkv); to_device(grad, dtype, d_do);
+  fa_b200_problem p{};
+  p.B = 1; p.H = G; p.Lq = L; p.Lk = L; p.D = D; p.dtype = dtype; p.causal = 1; p.softmax_scale = 1.f;
+  auto T = [&](void *base, int which) {
+    return fa_b200_tensor{(char *)base + which * GLD * es, (int64_t)GLD, (int64_t)L * D, (int64_t)D};
+  };
+  fa_b200_tensor q = T(d_qkv, 0), k = T(d_qkv, 1), v = T(d_qkv, 2), o = T(d_o, 0), dout = T(d_do, 0);
+  bool ok = fa_b200_fwd(&p, &q, &k, &v, &o, d_lse, nullptr) == 0;
+  const size_t wsb = fa_b200_bwd_workspace_bytes(&p);
+  CK(cudaMalloc(&d_ws, wsb));
+  fa_b200_tensor dq = T(d_a, 0), dk = T(d_a, 1), dv = T(d_a, 2);
+  ok = ok && fa_b200_bwd(&p, &q, &k, &v, &o, &dout, d_lse, &dq, &dk, &dv, d_ws, wsb, nullptr) == 0;
+  CK(cudaDeviceSynchronize());
+  const std::vector<float> want = from_device(d_a, 3 * GLD, dtype);
+  double worst_dq = 0;
+  for (int rep = 0; rep < 2 && ok; ++rep) {
+    CK(cudaMemset(d_b, 0xff, 3 * GLD * es));
+    fa_b200_tensor dq2 = T(d_b, 0), dk2 = T(d_b, 1), dv2 = T(d_b, 2);
+    const int rc = fa_b200_bwd_noalloc(&p, &q, &k, &v, &o, &dout, d_lse, &dq2, &dk2, &dv2, nullptr);
+    if (rc) { printf("  fa_b200_bwd_noalloc rc=%d: %s\n", rc, fa_b200_last_error()); ok = false; break; }
+    CK(cudaDeviceSynchronize());
+    const std::vector<float> got = from_device(d_b, 3 * GLD, dtype);
+    for (size_t i = GLD; i < 3 * GLD; ++i) if (got[i] != want[i]) { ok = false; break; }
+    worst_dq = std::max(worst_dq, max_abs_err(std::vector<float>(got.begin(), got.begin() + GLD), want.data(), GLD));
+  }
+  if (!(worst_dq <= 2e-2)) ok = false;
+  fa_b200_problem big = p;
+  big.H = 4096; big.Lq = big.Lk = 8192;  // far beyond FA_B200_NOALLOC_SCRATCH_BYTES: refused before anything is touched
+  if (fa_b200_bwd_noalloc(&big, &q, &k, &v, &o, &dout, d_lse, &dq, &dk, &dv, nullptr) != FA_B200_ERR_WORKSPACE) ok = false;
+  printf("%s noalloc G=%d L=%d D=%d %s : scratch %zu of %u bytes, max|dQ - dQ(fa_b200_bwd)|=%.3g, dK/dV identical\n",
+         ok ? "ok    " : "FAILED", G, L, D, dname(dtype), wsb, (unsigned)FA_B200_NOALLOC_SCRATCH_BYTES, worst_dq);
+  CK(cudaFree(d_qkv)); CK(cudaFree(d_o)); CK(cudaFree(d_do)); CK(cudaFree(d_a)); CK(cudaFree(d_b)); CK(cudaFree(d_lse));
+  CK(cudaFree(d_ws));
+  return ok;
+}
+
+TEST_CASE("backward with the static scratch equals backward with a workspace", "[attentionGrad][noalloc]") {
+  CHECK(run_noalloc_case(4, 1024, 128, FA_B200_BF16));
+  CHECK(run_noalloc_case(3, 331, 64, FA_B200_F16));
+}
+
 // tests/cpp/test_flash_attention.cpp:299-313 (prints a time per case to stderr; hidden: run with "[attentionperf]")
 TEST_CASE("benchmark flashAttention performance", "[.][attentionperf]") {
   SECTION("float32 8x256x256 cases") {
