@@ -6,7 +6,7 @@ import torch.nn.functional as F
 sys.path.insert(0, ".")
 import flash_attention_ipu.auto  # noqa: F401
 
-B, H, T, D = 4, 32, 2048, 128
+B, H, T, D = 4, 32, 2048, (int(sys.argv[1]) if len(sys.argv) > 1 else 128)
 q, k, v = (torch.randn(B, H, T, D, device="cuda", dtype=torch.bfloat16, requires_grad=True) for _ in range(3))
 g = torch.randn(B, H, T, D, device="cuda", dtype=torch.bfloat16)
 idx = torch.arange(T, device="cuda")
@@ -40,3 +40,9 @@ for name, kw, frac in [("non-causal", {}, 1.0), ("causal (is_causal)", {"is_caus
                        ("dropout 0.1 causal", {"dropout_p": 0.1, "is_causal": True}, 0.5)]:
     ms = timed(step(**kw))
     print(f"{name:34s} {ms:7.3f} ms  {flops * frac / ms / 1e9:7.1f} TFLOP/s (of the dense count)")
+
+# forward alone (no autograd), with and without the float bias
+with torch.no_grad():
+    for name, kw in [("forward only, no mask", {}), ("forward only, float bias", {"attn_mask": alibi})]:
+        ms = timed(lambda: F.scaled_dot_product_attention(q, k, v, **kw))
+        print(f"{name:34s} {ms:7.3f} ms")
