@@ -1022,3 +1022,42 @@ def test_item_order_chunks_do_not_change_a_group():
         assert torch.equal(o1[0], out[n]), n
         assert torch.equal(x1.grad[1, 0], x.grad[1, n]) and torch.equal(x1.grad[2, 0], x.grad[2, n]), n
         assert rel_fro(x1.grad[0, 0].float(), x.grad[0, n].float()) < 1e-3, n
+
+
+@pytest.mark.parametrize("H,Hkv,D,causal,dtype,lens_q,lens_k", [
+    (4, 2, 64, True, "bf16", [200, 1, 331, 128], [200, 1, 331, 128]),     # self-attention, grouped-query
+    (2, 2, 128, False, "fp16", [130, 64, 257], [72, 264, 8]),             # cross-attention lengths, non-causal
+    (3, 3, 40, True, "fp32", [50, 77], [50, 77]),                          # SIMT family through the same views
+])
+def test_varlen_packed_tokens(H, Hkv, D, causal, dtype, lens_q, lens_k):
+    """flash_attention_ipu_b200.varlen: sequences packed along the token axis, one strided-view problem per
+    sequence written in place -- each sequence equals fp64 attention of that sequence alone, and no token of one
+    sequence influences another."""
+    from flash_attention_ipu_b200.varlen import flash_attention_varlen
+    torch.manual_seed(SEED + D)
+    dt = DT[dtype]
+    tq, tk = sum(lens_q), sum(lens_k)
+    q, dout = (torch.randn(tq, H, D).to(dt) for _ in range(2))
+    k, v = (torch.randn(tk, Hkv, D).to(dt) for _ in range(2))
+    cq = [0] + list(np.cumsum(lens_q))
+    ck = torch.tensor([0] + list(np.cumsum(lens_k)), dtype=torch.int32)   # a tensor works as well as a list
+    xs = [t.cuda().requires_grad_(True) for t in (q, k, v)]
+    out = flash_attention_varlen(*xs, cq, ck, causal=causal)
+    out.backward(dout.cuda())
+    torch.cuda.synchronize()
+    tol_o, tol_g = (1e-4, 1e-4) if dtype == "fp32" else (1e-2, 1e-2)
+    for s in range(len(lens_q)):
+        q0, q1, k0, k1 = cq[s], cq[s + 1], int(ck[s]), int(ck[s + 1])
+        bhld = lambda t, a, b: t[a:b].permute(1, 0, 2)[None].float()
+        ref = _blocked_reference(bhld(q, q0, q1), bhld(k, k0, k1).repeat_interleave(H // Hkv, 1),
+                                 bhld(v, k0, k1).repeat_interleave(H // Hkv, 1), bhld(dout, q0, q1), causal, 0, D ** -0.5)
+        got = out.detach()[q0:q1].permute(1, 0, 2)[None].float().cpu().double()
+        assert (got - ref[0]).abs().max().item() <= tol_o * 2, s
+        # a one-token sequence has dq = 0 exactly (softmax of one score): absolute bound where the reference vanishes
+        close = lambda a, b: rel_fro(a, b) < tol_g or (a - b).abs().max().item() < 1e-6
+        assert close(xs[0].grad[q0:q1].permute(1, 0, 2)[None].float().cpu().double(), ref[2]), s
+        for x, r in ((xs[1], ref[3]), (xs[2], ref[4])):
+            want = r.view(1, Hkv, H // Hkv, k1 - k0, D).sum(2)            # query heads that share a K/V head
+            assert close(x.grad[k0:k1].permute(1, 0, 2)[None].float().cpu().double(), want), s
+    with pytest.raises(ValueError):
+        flash_attention_varlen(*xs, [0, tq - 1], ck)

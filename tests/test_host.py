@@ -117,3 +117,15 @@ def test_ops_library_registers_the_four_ops():
         ops.attention_fwd(x, x, x, 1.0, True, 0, 0)
     with pytest.raises(RuntimeError, match="no CPU path"):
         ops.qkv_packed_bwd(x[0], torch.randn(3, 2, 8, 8), x[0], torch.randn(2, 8), 1.0, True, 0, 0)
+
+
+def test_varlen_argument_checks():
+    """flash_attention_ipu_b200/varlen.py refuses malformed boundaries and CPU tensors (there is no CPU path)."""
+    from flash_attention_ipu_b200.varlen import flash_attention_varlen
+    q = torch.randn(10, 2, 64)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        flash_attention_varlen(q, q, q, [0, 4, 10], [0, 4, 10])
+    with pytest.raises(ValueError):
+        flash_attention_varlen(q, q, q[:, :, :32], [0, 10], [0, 10])
+    with pytest.raises(ValueError):
+        flash_attention_varlen(q, q, q, [1, 10], [0, 10])
