@@ -11,8 +11,12 @@
  * Conventions
  *  - every function returns 0 on success, a negative fa_b200_status otherwise;
  *    fa_b200_last_error() gives a thread-local message for the last failure.
- *  - the library never allocates or frees device memory, never synchronises the
- *    device and only enqueues work on the stream it is given (cudaStream_t as void*).
+ *  - the library never allocates or frees device memory (its own state on the device is two
+ *    static arrays: the work counters of the persistent forward and the scratch of
+ *    fa_b200_bwd_noalloc), never synchronises the device (fa_b200_bwd_sm_clock, a
+ *    measurement hook, excepted) and only enqueues work on the stream it is given
+ *    (cudaStream_t as void*).  The tcgen05 kernels are launched with programmatic stream
+ *    serialization among themselves (FA_B200_PDL=0 in the environment: plain launches).
  *  - the caller makes the tensors' device current before the call.
  *  - tensors are 4-D (B, H, L, D) with D contiguous; strides are in ELEMENTS.
  *    The packed (3,G,L,D) layout of the reference API is B=1, H=G,
