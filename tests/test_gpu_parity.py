@@ -1127,3 +1127,34 @@ def test_two_streams_and_graph_replay():
         torch.cuda.synchronize()
         assert torch.equal(o, serial[0][0]) and torch.equal(dk, serial[0][2]) and torch.equal(dv, serial[0][3]), rep
         assert rel_fro(dq.float(), serial[0][1].float()) < 1e-3, rep
+
+
+def test_dropout_with_key_padding():
+    """kv_lens and dropout together (the usual BERT-style training call: padding mask + attention dropout): the
+    padded keys are outside the softmax, the surviving ones are thinned by the hash mask."""
+    native = _native_loaded()
+    torch.manual_seed(SEED)
+    B, H, L, D, p_drop, seed = 2, 2, 384, 64, 0.2, 77
+    lens = [384, 150]
+    q, k, v, dout = (torch.randn(B, H, L, D).bfloat16() for _ in range(4))
+    keep, drop_scale = ao.dropout_keep_mask(seed, B * H, L, L, p_drop)
+    keep = keep.view(B, H, L, L)
+    valid = (torch.arange(L)[None, :] < torch.tensor(lens)[:, None])            # (B, L)
+    qd, kd, vd = (t.double().requires_grad_(True) for t in (q, k, v))
+    s = torch.einsum("bhqd,bhkd->bhqk", qd, kd) * D ** -0.5
+    s = s.masked_fill(~valid[:, None, None, :], float("-inf"))
+    ref = torch.einsum("bhqk,bhkd->bhqd", torch.softmax(s, -1) * keep.double() * drop_scale, vd)
+    ref.backward(dout.double())
+    xs = [t.cuda() for t in (q, k, v, dout)]
+    lens_t = torch.tensor(lens, dtype=torch.int32).repeat_interleave(H).cuda()
+    prob = native.make_problem(xs[0], xs[1], False, D ** -0.5, kv_lens=lens_t, dropout_p=p_drop, dropout_seed=seed)
+    o, lse = torch.empty_like(xs[0]), torch.empty(B, H, L, device="cuda", dtype=torch.float32)
+    native.fwd(prob, xs[0], xs[1], xs[2], o, lse)
+    dq, dk, dv = (torch.empty_like(t) for t in xs[:3])
+    ws = torch.empty(native.bwd_workspace_bytes(prob), device="cuda", dtype=torch.uint8)
+    native.bwd(prob, xs[0], xs[1], xs[2], o, xs[3], lse, dq, dk, dv, ws)
+    torch.cuda.synchronize()
+    assert rel_fro(o.cpu().double(), ref.detach()) < 1e-2
+    for got, want in zip((dq, dk, dv), (qd.grad, kd.grad, vd.grad)):
+        assert rel_fro(got.cpu().double(), want) < 1e-2
+    assert torch.count_nonzero(dk[1, :, 150:]) == 0 and torch.count_nonzero(dv[1, :, 150:]) == 0
