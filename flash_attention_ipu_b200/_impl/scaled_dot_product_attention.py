@@ -98,8 +98,6 @@ def _sdpa_impl(
             raise NotImplementedError(
                 "flash_attention_ipu supports attn_mask only for 4-D bf16 / fp16 CUDA tensors with D in {64, 128}: "
                 "a boolean or float mask broadcastable to (B, H, Lq, Lk) with Lk % 8 == 0 and no gradient")
-        if bias is not None and dropout_p > 0.0:
-            raise NotImplementedError("flash_attention_ipu does not support attn_mask together with dropout_p > 0")
     dropout_seed = 0
     if dropout_p > 0.0:
         # The reference refuses dropout (:25-28).  Here the tcgen05 kernels apply it (16-bit, D in {64, 128});

@@ -97,7 +97,6 @@ int check_problem(const fa_b200_problem *p) {
   if (p->bias) {
     if (!(p->dtype != FA_B200_F32 && (p->D == 64 || p->D == 128)))
       return fail(FA_B200_ERR_UNSUPPORTED, "an additive bias needs the tensor path (16-bit, D in {64,128})");
-    if (p->dropout_p > 0.f) return fail(FA_B200_ERR_UNSUPPORTED, "bias and dropout together are not supported");
     if (p->Lk % 8 || reinterpret_cast<uintptr_t>(p->bias) % 16 || p->bias_stride_l % 8 || p->bias_stride_h % 8 ||
         p->bias_stride_b % 8 || (p->bias_stride_l != 0 && p->bias_stride_l < p->Lk) || p->bias_stride_h < 0 ||
         p->bias_stride_b < 0)
@@ -473,10 +472,10 @@ int tensor_fwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const bool bias = p->bias != nullptr;
   fp.bias = reinterpret_cast<const uint16_t *>(p->bias);
   fp.bias_sb = p->bias_stride_b; fp.bias_sh = p->bias_stride_h; fp.bias_sl = p->bias_stride_l;
-  auto kern = bias ? fa::fa_fwd_sm100_kernel<D, kBf16, false, true>
-              : drop ? fa::fa_fwd_sm100_kernel<D, kBf16, true, false> : fa::fa_fwd_sm100_kernel<D, kBf16, false, false>;
-  static std::atomic<uint64_t> smem_ok[3] = {{0}, {0}, {0}};  // per instantiation
-  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok[bias ? 2 : drop])) return rc;
+  auto kern = bias ? (drop ? fa::fa_fwd_sm100_kernel<D, kBf16, true, true> : fa::fa_fwd_sm100_kernel<D, kBf16, false, true>)
+                   : (drop ? fa::fa_fwd_sm100_kernel<D, kBf16, true, false> : fa::fa_fwd_sm100_kernel<D, kBf16, false, false>);
+  static std::atomic<uint64_t> smem_ok[4] = {{0}, {0}, {0}, {0}};  // per instantiation
+  if (int rc = allow_smem(kern, fa::FwdSmem<D>::kAlloc, smem_ok[drop + 2 * bias])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory); with no more items
   // than SMs every CTA runs exactly one and no counter is needed
   const int sms = sm_count();
@@ -556,11 +555,15 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   const bool bias = p->bias != nullptr;
   bp.bias = reinterpret_cast<const uint16_t *>(p->bias);
   bp.bias_sb = p->bias_stride_b; bp.bias_sh = p->bias_stride_h; bp.bias_sl = p->bias_stride_l;
-  auto kern = bias   ? (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, false, true> : fa::fa_bwd_sm100_kernel<D, kBf16, false, false, true>)
-              : drop ? (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, true, false> : fa::fa_bwd_sm100_kernel<D, kBf16, false, true, false>)
-                     : (gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, false, false> : fa::fa_bwd_sm100_kernel<D, kBf16, false, false, false>);
-  static std::atomic<uint64_t> smem_ok[6] = {{0}, {0}, {0}, {0}, {0}, {0}};
-  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * (bias ? 2 : drop)])) return rc;
+  auto pick = [&](auto drop_c, auto bias_c) {
+    constexpr bool kD = decltype(drop_c)::value, kB = decltype(bias_c)::value;
+    return gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, kD, kB> : fa::fa_bwd_sm100_kernel<D, kBf16, false, kD, kB>;
+  };
+  using T_ = std::true_type;
+  using F_ = std::false_type;
+  auto kern = bias ? (drop ? pick(T_{}, T_{}) : pick(F_{}, T_{})) : (drop ? pick(T_{}, F_{}) : pick(F_{}, F_{}));
+  static std::atomic<uint64_t> smem_ok[8] = {{0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}};
+  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * drop + 4 * bias])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory), items by atomic counter
   const unsigned grid = (unsigned)(items < sm_count() ? items : sm_count());
 #ifdef FA_BWD_TRACE

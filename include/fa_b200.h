@@ -81,8 +81,7 @@ typedef struct {
                          /* _impl/scaled_dot_product_attention.py:21-24): S' = scale*q.k + bias[b][h][q][k], */
                          /* elements of `dtype`, -inf = masked.  Element strides below; 0 broadcasts the   */
                          /* batch / head / query dim; the key dim has unit stride.  Tensor path only; Lk % 8 == 0, */
-                         /* 16-byte aligned pointer and row stride; not together with dropout; no gradient */
-                         /* is produced for the bias.                                                      */
+                         /* 16-byte aligned pointer and row stride; no gradient is produced for the bias.   */
   int64_t bias_stride_b, bias_stride_h, bias_stride_l;
 } fa_b200_problem;
 

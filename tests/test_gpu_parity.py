@@ -938,10 +938,25 @@ def test_additive_bias_through_the_c_abi(B, H, Hkv, Lq, Lk, D, causal, dtype, bs
     assert rel_fro(o.cpu().double(), ref[0]) < 1e-2
     for got, want in zip((dq, dk, dv), (ref[2], ref[3], ref[4])):
         assert rel_fro(got.cpu().double(), want) < 1e-2
-    # refused: Lk not a multiple of 8, bias together with dropout, bias off the tensor path
-    with pytest.raises(RuntimeError, match="bias"):
-        bad = native.make_problem(qd, kd, causal, scale, bias=bd, dropout_p=0.1)
-        native.fwd(bad, qd, kd, vd, o, lse)
+    # bias AND dropout (T5-style training): the same fp64 math with the oracle's keep mask on the probabilities
+    seed, p_drop = 4242, 0.25
+    keep, drop_scale = ao.dropout_keep_mask(seed, B * H, Lq, Lk, p_drop)
+    x64 = [t.double().requires_grad_(True) for t in (q, k, v)]
+    rep_kv = H // Hkv
+    s64 = torch.einsum("bhqd,bhkd->bhqk", x64[0], x64[1].repeat_interleave(rep_kv, 1)) * scale + bias.double().expand(B, H, Lq, Lk)
+    if causal:
+        s64 = s64.masked_fill(torch.arange(Lk)[None, :] > torch.arange(Lq)[:, None], float("-inf"))
+    ref_d = torch.einsum("bhqk,bhkd->bhqd", torch.softmax(s64, -1) * keep.view(B, H, Lq, Lk).double() * drop_scale,
+                         x64[2].repeat_interleave(rep_kv, 1))
+    ref_d.backward(dout.double())
+    prob_d = native.make_problem(qd, kd, causal, scale, bias=bd, dropout_p=p_drop, dropout_seed=seed)
+    native.fwd(prob_d, qd, kd, vd, o, lse)
+    native.bwd(prob_d, qd, kd, vd, o, dd, lse, dq, dk, dv, ws)
+    torch.cuda.synchronize()
+    assert rel_fro(o.cpu().double(), ref_d.detach()) < 1e-2
+    for got, want in zip((dq, dk, dv), x64):
+        assert rel_fro(got.cpu().double(), want.grad) < 1e-2
+    # refused: Lk not a multiple of 8, bias off the tensor path
     k7 = kd[:, :, :Lk - 1].contiguous()
     with pytest.raises(RuntimeError, match="bias"):
         bad = native.make_problem(qd, k7, causal, scale, bias=torch.zeros(B, H, Lq, Lk - 1, device="cuda", dtype=dt))
@@ -991,11 +1006,12 @@ def test_attn_mask_through_sdpa_override():
         out = F.scaled_dot_product_attention(*ys, attn_mask=left.cuda())
         ref = orig(q.float(), k.float(), v.float(), attn_mask=left)
         assert (out.float().cpu() - ref).abs().max().item() <= 2e-2
-        # a mask that wants a gradient, or together with dropout, keeps the reference's refusal
+        # a mask that wants a gradient keeps the reference's refusal; a mask together with dropout runs on our kernels
         with pytest.raises(NotImplementedError):
             F.scaled_dot_product_attention(*ys, attn_mask=torch.zeros(L, L, device="cuda", dtype=torch.bfloat16, requires_grad=True))
-        with pytest.raises(NotImplementedError, match="dropout"):
-            F.scaled_dot_product_attention(*ys, attn_mask=band.cuda(), dropout_p=0.1)
+        before = native.launch_count()
+        both = F.scaled_dot_product_attention(*ys, attn_mask=band.cuda(), dropout_p=0.1)
+        assert native.launch_count() > before and torch.isfinite(both.float()).all()
     finally:
         mod.KEY_PADDING_FAST_PATH = True
         mod.uninstall()
