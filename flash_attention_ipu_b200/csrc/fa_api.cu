@@ -556,14 +556,21 @@ int tensor_bwd(const fa_b200_problem *p, const fa_b200_tensor *q, const fa_b200_
   bp.bias = reinterpret_cast<const uint16_t *>(p->bias);
   bp.bias_sb = p->bias_stride_b; bp.bias_sh = p->bias_stride_h; bp.bias_sl = p->bias_stride_l;
   auto pick = [&](auto drop_c, auto bias_c) {
-    constexpr bool kD = decltype(drop_c)::value, kB = decltype(bias_c)::value;
+    constexpr bool kD = decltype(drop_c)::value;
+    constexpr int kB = decltype(bias_c)::value;
     return gqa ? fa::fa_bwd_sm100_kernel<D, kBf16, true, kD, kB> : fa::fa_bwd_sm100_kernel<D, kBf16, false, kD, kB>;
   };
   using T_ = std::true_type;
   using F_ = std::false_type;
-  auto kern = bias ? (drop ? pick(T_{}, T_{}) : pick(F_{}, T_{})) : (drop ? pick(T_{}, F_{}) : pick(F_{}, F_{}));
-  static std::atomic<uint64_t> smem_ok[8] = {{0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}};
-  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * drop + 4 * bias])) return rc;
+  using B0 = std::integral_constant<int, 0>;
+  using B1 = std::integral_constant<int, 1>;
+  using B2 = std::integral_constant<int, 2>;
+  const int bias_mode = !bias ? 0 : p->bias_stride_l == 0 ? 2 : 1;  // 2: one bias row for every query (key mask)
+  auto kern = bias_mode == 2 ? (drop ? pick(T_{}, B2{}) : pick(F_{}, B2{}))
+              : bias_mode == 1 ? (drop ? pick(T_{}, B1{}) : pick(F_{}, B1{}))
+                               : (drop ? pick(T_{}, B0{}) : pick(F_{}, B0{}));
+  static std::atomic<uint64_t> smem_ok[12] = {{0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}, {0}};
+  if (int rc = allow_smem(kern, fa::BwdSmem<D>::kBytes, smem_ok[gqa + 2 * drop + 4 * bias_mode])) return rc;
   // persistent: one CTA per SM (the kernel takes all of an SM's shared memory), items by atomic counter
   const unsigned grid = (unsigned)(items < sm_count() ? items : sm_count());
 #ifdef FA_BWD_TRACE

@@ -187,7 +187,9 @@ __device__ __forceinline__ void bwd_next_tile(int &h, int &i, int i0, int num_q_
 // kDrop = dropout on P: with M the keep mask and s = 1 / (1 - p), the forward computed O = s (M o P) V, so
 //   dV = s (M o P)^T dO   (the thinned P^T is the A operand; s is applied once, at the item's end)
 //   dS = P o (s M o dP - delta)   with delta = rowsum(O o dO) as before and P the UNdropped softmax.
-template <int D, bool kBf16, bool kGqa, bool kDrop = false, bool kBias = false>
+// kBias: 0 none, 1 one bias row per query (general), 2 one bias row for every query (row stride 0: a key mask /
+// key bias -- a single load per thread and tile instead of 64)
+template <int D, bool kBf16, bool kGqa, bool kDrop = false, int kBias = 0>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -542,6 +544,12 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           // warp read 32 neighbouring keys of one query row (one 64-byte segment per load)
           const uint16_t *bcol = p.bias + t.b * p.bias_sb + (t.h0 + hx) * p.bias_sh + key;
           const int q0 = i * 128 + 64 * wg;
+          if (kBias == 2) {
+            // one bias row for every query (a key mask / key bias): a single load per thread and tile
+            const float bk = key < p.Lk ? unpack1<kBf16>(__ldg(bcol)) * kLog2e : 0.f;
+            #pragma unroll
+            for (int c = 0; c < 64; ++c) nl[c] += bk;
+          } else {
           // two batches of 32 independent loads (all issued before the first is used), each under the wait for S^T
           #pragma unroll
           for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -566,6 +574,7 @@ fa_bwd_sm100_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(bcol - lane + static_cast<long long>(qn) * p.bias_sl));
             }
           }
+          }  // general (per-query) bias
         }
         // dropout: bit c of keepm = query column c of this warpgroup keeps this thread's key (generated
         // ahead of the S^T wait; sm100_ptx.cuh: drop_hash).  Thread <-> key, and one hash word covers the 4

@@ -13,6 +13,7 @@ idx = torch.arange(T, device="cuda")
 alibi = (-0.05 * (idx[:, None] - idx[None, :]).abs().float())[None, None].expand(1, H, T, T).bfloat16().contiguous()
 causal_bool = (idx[None, :] <= idx[:, None])
 pad = (idx[None, :] < torch.tensor([2048, 1500, 1024, 700], device="cuda")[:, None]).view(B, 1, 1, T)
+left = torch.zeros(B, 1, 1, T, device="cuda", dtype=torch.bfloat16).masked_fill_(~pad.flip(-1), float("-inf"))  # float key mask: (B, 1, 1, T), one row for every query
 flops = 4.0 * B * H * T * T * D * 3.5
 
 
@@ -36,7 +37,8 @@ def step(**kw):
 
 for name, kw, frac in [("non-causal", {}, 1.0), ("causal (is_causal)", {"is_causal": True}, 0.5),
                        ("float bias (1,H,T,T)", {"attn_mask": alibi}, 1.0), ("bool causal mask (T,T) as bias", {"attn_mask": causal_bool}, 1.0),
-                       ("key padding (kv_lens)", {"attn_mask": pad}, 1.0), ("dropout 0.1", {"dropout_p": 0.1}, 1.0),
+                       ("key padding (kv_lens)", {"attn_mask": pad}, 1.0), ("left padding (key mask as bias)", {"attn_mask": left}, 1.0),
+                       ("dropout 0.1", {"dropout_p": 0.1}, 1.0),
                        ("dropout 0.1 causal", {"dropout_p": 0.1, "is_causal": True}, 0.5)]:
     ms = timed(step(**kw))
     print(f"{name:34s} {ms:7.3f} ms  {flops * frac / ms / 1e9:7.1f} TFLOP/s (of the dense count)")
