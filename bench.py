@@ -449,7 +449,9 @@ def run_ours(args):
     from flash_attention_ipu_b200.streaming import HostStreamedAttention
     # chunk of 4 groups (32 MiB up, 32 MiB down): measured 23.7-24.1 ms per step against 25.9 with 8, 26.1 with 16 and
     # 28.9 with 2 (host-bound) -- the pipeline's fill and drain are one chunk each
-    gpc = 4 if Gl % 4 == 0 else 1
+    # (one rank; with several ranks the host side is shared and fewer, larger chunks win: 16.4 ms with 8 against 19.1 ms
+    # with 4 at N=8)
+    gpc = (4 if world == 1 else 8) if Gl % 8 == 0 else (4 if Gl % 4 == 0 else 1)
     if os.environ.get("FA_E2E_GPC"):  # chunk-size probe
         gpc = int(os.environ["FA_E2E_GPC"])
     pipe = HostStreamedAttention(Gl, T, D, torch.bfloat16, dev, groups_per_chunk=gpc, num_chunks_q=ncq, num_chunks_kv=nckv,
